@@ -1,0 +1,397 @@
+// Stage 2a of the rasteriser: key duplication, stable LSD radix sort
+// ("onesweep": one read + one write of the pairs per digit, chained-scan
+// decoupled look-back across tiles), and tile range detection.
+//
+// Replaces duplicateWithKeys (DGR/cuda_rasterizer/rasterizer_impl.cu:70-111),
+// the call into cub::DeviceRadixSort::SortPairs (:303-308; CUB is a CUDA
+// toolkit dependency, not vendored — the contract is "stable sort on key bits
+// [0, 32+bit)", which is what this file implements), and identifyTileRanges
+// (:116-138).  Key layout is the reference's: (tile_id << 32) | float_bits(depth).
+//
+// What differs from the reference's structure:
+//  * duplication is slot-centric: a CTA owns a contiguous range of output
+//    slots (its 256 Gaussians' prefix-sum interval) and each thread fills slots
+//    s, s+256, ... after a binary search for the owning Gaussian.  Writes are
+//    fully coalesced and a huge splat is spread over the whole CTA instead of
+//    being looped over by one thread.
+//  * the digit histograms of ALL sort passes are accumulated while the keys
+//    are produced (shared-memory atomics), so the sort never re-reads the keys
+//    for a separate histogram kernel.
+//  * the element count lives in device memory; grids are sized by the buffer
+//    capacity and surplus CTAs exit, so no host round-trip is needed.
+#include "common.cuh"
+
+namespace ggd {
+
+namespace {
+
+constexpr int kDupThreads = 256;
+static_assert(kSortThreads == kRadixBins, "one thread per digit in the look-back");
+
+// ---------------------------------------------------------------------------
+// duplicate
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(kDupThreads)
+duplicate_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ means2D,
+                 const float* __restrict__ depths, const uint32_t* __restrict__ offsets,
+                 const int* __restrict__ radii, uint64_t* __restrict__ keys,
+                 uint32_t* __restrict__ vals, uint32_t capacity, uint32_t* __restrict__ counters,
+                 uint32_t* __restrict__ hist, int num_passes)
+{
+    __shared__ uint32_t s_end[kDupThreads];
+    __shared__ uint32_t s_depth[kDupThreads];
+    __shared__ uint32_t s_rect[kDupThreads];  // x0 | y0 << 16 (tile coordinates, each < 65536)
+    __shared__ uint32_t s_w[kDupThreads];
+    __shared__ uint32_t s_hist[kMaxSortPasses][kRadixBins];
+
+    const int t = threadIdx.x;
+    const int base = blockIdx.x * kDupThreads;
+    const int idx = base + t;
+    for (int i = t; i < num_passes * kRadixBins; i += kDupThreads) (&s_hist[0][0])[i] = 0;
+
+    const uint32_t block_start = (base == 0) ? 0u : __ldg(offsets + base - 1);
+    uint32_t my_end = 0;
+    if (idx < P) {
+        my_end = __ldg(offsets + idx);
+        const int r = __ldg(radii + idx);
+        uint32_t x0 = 0, y0 = 0, w = 0;
+        if (r > 0) {
+            uint2 rmin, rmax;
+            tile_rect(__ldg(means2D + idx), r, grid_x, grid_y, rmin, rmax);
+            x0 = rmin.x; y0 = rmin.y; w = rmax.x - rmin.x;
+            s_depth[t] = __float_as_uint(__ldg(depths + idx));
+        }
+        s_rect[t] = x0 | (y0 << 16);
+        s_w[t] = w;
+    }
+    s_end[t] = (idx < P) ? my_end : 0xffffffffu;
+    __syncthreads();
+    const int last = min(kDupThreads, P - base) - 1;
+    const uint32_t block_end = s_end[last];
+
+    if (blockIdx.x == 0 && t == 0) {
+        const uint32_t R = __ldg(offsets + P - 1);
+        counters[3] = min(R, capacity);  // element count the sort and the range kernel use
+        counters[1] = (R > capacity) ? 1u : 0u;
+    }
+
+    for (uint32_t s = block_start + t; s < block_end; s += kDupThreads) {
+        // first g with s_end[g] > s
+        int lo = 0, hi = last;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int mid = (lo + hi) >> 1;
+            if (s_end[mid] > s) hi = mid; else lo = mid + 1;
+        }
+        const int g = lo;
+        const uint32_t g_start = (g == 0) ? block_start : s_end[g - 1];
+        const uint32_t j = s - g_start;
+        const uint32_t w = s_w[g];
+        const uint32_t rc = s_rect[g];
+        const uint32_t y = (rc >> 16) + j / w;
+        const uint32_t x = (rc & 0xffffu) + j % w;
+        uint64_t key = (uint64_t)(y * (uint32_t)grid_x + x);
+        key <<= 32;
+        key |= s_depth[g];
+        if (s < capacity) {
+            keys[s] = key;
+            vals[s] = (uint32_t)(base + g);
+#pragma unroll
+            for (int p = 0; p < kMaxSortPasses; ++p)
+                if (p < num_passes) atomicAdd(&s_hist[p][(key >> (p * kRadixBits)) & (kRadixBins - 1)], 1u);
+        }
+    }
+    __syncthreads();
+    for (int i = t; i < num_passes * kRadixBins; i += kDupThreads) {
+        const uint32_t c = (&s_hist[0][0])[i];
+        if (c) atomicAdd(hist + i, c);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// stand-alone histogram (ggd_sort_pairs entry point, keys not produced by us)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+histogram_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ n_ptr,
+                 uint32_t capacity, int begin_bit, int end_bit, int num_passes,
+                 uint32_t* __restrict__ hist)
+{
+    __shared__ uint32_t s_hist[kMaxSortPasses][kRadixBins];
+    const uint32_t n = min(__ldg(n_ptr), capacity);
+    for (int i = threadIdx.x; i < num_passes * kRadixBins; i += 256) (&s_hist[0][0])[i] = 0;
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < n; i += gridDim.x * 256u) {
+        const uint64_t key = __ldg(keys + i);
+        for (int p = 0; p < num_passes; ++p) {
+            const int shift = begin_bit + p * kRadixBits;
+            const int bits = min(kRadixBits, end_bit - shift);
+            atomicAdd(&s_hist[p][(key >> shift) & ((1u << bits) - 1u)], 1u);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < num_passes * kRadixBins; i += 256) {
+        const uint32_t c = (&s_hist[0][0])[i];
+        if (c) atomicAdd(hist + i, c);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// onesweep digit pass
+// ---------------------------------------------------------------------------
+constexpr uint32_t kLbAgg = 1u << 30;
+constexpr uint32_t kLbPre = 2u << 30;
+constexpr uint32_t kLbMask = (1u << 30) - 1u;
+constexpr int kSortWarps = kSortThreads / 32;
+
+// exclusive scan of one value per thread over the 256-thread CTA
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp /*[8]*/)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+    }
+    __syncthreads();  // protect s_warp reuse
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t off = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w)
+        if (w < warp) off += s_warp[w];
+    return off + incl - v;
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
+                const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
+                const uint32_t* __restrict__ n_ptr, uint32_t capacity, int shift, uint32_t mask,
+                const uint32_t* __restrict__ hist /*[256] digit counts of this pass*/,
+                uint32_t* __restrict__ lookback /*[tiles][256]*/, uint32_t* __restrict__ ticket)
+{
+    __shared__ __align__(16) uint64_t s_keys[kSortTile];       // 32 KB, reused for values
+    __shared__ uint32_t s_whist[kSortWarps][kRadixBins];        // 8 KB
+    __shared__ uint32_t s_gbase[kRadixBins];
+    __shared__ uint32_t s_loff[kRadixBins];
+    __shared__ uint32_t s_scan[kSortWarps];
+    __shared__ uint32_t s_tile;
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t == 0) s_tile = atomicAdd(ticket, 1u);
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) s_whist[w][t] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t n = min(__ldg(n_ptr), capacity);
+    const uint64_t tile_base = (uint64_t)tile * kSortTile;
+    if (tile_base >= n) return;
+    const uint32_t n_valid = (uint32_t)min((uint64_t)kSortTile, (uint64_t)n - tile_base);
+
+    // ---- load (warp-striped: item k of lane l sits at warp_base + k*32 + l)
+    uint64_t key[kSortItems];
+    const uint32_t warp_base = warp * (32 * kSortItems);
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const uint32_t li = warp_base + k * 32 + lane;
+        key[k] = (li < n_valid) ? __ldg(keys_in + tile_base + li) : ~0ull;
+    }
+
+    // ---- stable in-warp ranking, digit by digit position (k outer)
+    uint16_t rank[kSortItems];
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const uint32_t li = warp_base + k * 32 + lane;
+        const uint32_t d = (li < n_valid) ? (uint32_t)((key[k] >> shift) & mask) : (kRadixBins - 1);
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t prior = s_whist[warp][d];
+        __syncwarp();
+        if ((peers & ((1u << lane) - 1u)) == 0) s_whist[warp][d] = prior + __popc(peers);
+        __syncwarp();
+        rank[k] = (uint16_t)(prior + __popc(peers & ((1u << lane) - 1u)));
+    }
+    __syncthreads();
+
+    // ---- per digit (thread t == digit t): warp counts -> warp-exclusive offsets, CTA total
+    uint32_t total = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) {
+        const uint32_t c = s_whist[w][t];
+        s_whist[w][t] = total;
+        total += c;
+    }
+    uint32_t count = total;
+    if (t == kRadixBins - 1) count -= (kSortTile - n_valid);  // padding items are not real
+
+    // ---- publish aggregate, look back for the exclusive prefix of this digit
+    uint32_t* my_lb = lookback + (size_t)tile * kRadixBins + t;
+    uint32_t excl = 0;
+    if (tile == 0) {
+        atomicExch(my_lb, kLbPre | count);
+    } else {
+        atomicExch(my_lb, kLbAgg | count);
+        int look = (int)tile - 1;
+        while (true) {
+            const uint32_t w = *reinterpret_cast<volatile uint32_t*>(lookback + (size_t)look * kRadixBins + t);
+            const uint32_t f = w >> 30;
+            if (f == 0) continue;
+            excl += w & kLbMask;
+            if (f == 2) break;
+            --look;
+        }
+        atomicExch(my_lb, kLbPre | (excl + count));
+    }
+
+    // ---- digit bases: global (from the whole-array histogram) and CTA-local
+    const uint32_t g_excl = block_excl_scan(__ldg(hist + t), s_scan);
+    const uint32_t l_excl = block_excl_scan(total, s_scan);
+    s_loff[t] = l_excl;
+    s_gbase[t] = g_excl + excl - l_excl;
+    __syncthreads();
+
+    // ---- local reorder through shared memory, then coalesced scatter
+    uint16_t lpos[kSortItems];
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const uint32_t li = warp_base + k * 32 + lane;
+        const uint32_t d = (li < n_valid) ? (uint32_t)((key[k] >> shift) & mask) : (kRadixBins - 1);
+        lpos[k] = (uint16_t)(s_loff[d] + s_whist[warp][d] + rank[k]);
+        s_keys[lpos[k]] = key[k];
+    }
+    __syncthreads();
+    uint32_t gpos[kSortItems];
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const uint32_t i = t + k * kSortThreads;
+        if (i < n_valid) {
+            const uint64_t kk = s_keys[i];
+            const uint32_t d = (uint32_t)((kk >> shift) & mask);
+            gpos[k] = s_gbase[d] + i;
+            keys_out[gpos[k]] = kk;
+        }
+    }
+    __syncthreads();
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys);
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const uint32_t li = warp_base + k * 32 + lane;
+        if (li < n_valid) s_vals[lpos[k]] = __ldg(vals_in + tile_base + li);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const uint32_t i = t + k * kSortThreads;
+        if (i < n_valid) vals_out[gpos[k]] = s_vals[i];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// tile ranges
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(const uint32_t* __restrict__ n_ptr, const uint64_t* __restrict__ keys,
+                   uint2* __restrict__ ranges)
+{
+    const uint32_t L = __ldg(n_ptr);
+    for (uint32_t idx = blockIdx.x * 256u + threadIdx.x; idx < L; idx += gridDim.x * 256u) {
+        const uint32_t cur = (uint32_t)(__ldg(keys + idx) >> 32);
+        if (idx == 0) {
+            ranges[cur].x = 0;
+        } else {
+            const uint32_t prev = (uint32_t)(__ldg(keys + idx - 1) >> 32);
+            if (cur != prev) {
+                ranges[prev].y = idx;
+                ranges[cur].x = idx;
+            }
+        }
+        if (idx == L - 1) ranges[cur].y = L;
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+SortScratch carve_sort_scratch(void* base, uint64_t capacity)
+{
+    SortScratch sc;
+    const size_t tiles = (size_t)((capacity + kSortTile - 1) / kSortTile) + 1;
+    char* p = static_cast<char*>(base);
+    size_t off = 0;
+    sc.hist = reinterpret_cast<uint32_t*>(p + off);
+    off += align_up(sizeof(uint32_t) * kMaxSortPasses * kRadixBins, 256);
+    sc.tickets = reinterpret_cast<uint32_t*>(p + off);
+    off += 256;
+    sc.lookback = reinterpret_cast<uint32_t*>(p + off);
+    off += align_up(sizeof(uint32_t) * kMaxSortPasses * tiles * kRadixBins, 256);
+    sc.bytes = off;
+    sc.zero_bytes = off;
+    return sc;
+}
+
+int sort_pairs(cudaStream_t s, const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
+               uint32_t* vals_out, const uint32_t* n_dev, uint64_t capacity, int begin_bit,
+               int end_bit, uint64_t* keys_tmp, uint32_t* vals_tmp, const SortScratch& sc,
+               bool hist_precomputed)
+{
+    if (capacity >= (1ull << 30)) {
+        set_error("sort_pairs: capacity %llu exceeds 2^30-1", (unsigned long long)capacity);
+        return GGD_E_INVALID;
+    }
+    if (begin_bit < 0 || end_bit > 64 || end_bit <= begin_bit) {
+        set_error("sort_pairs: bad bit range [%d,%d)", begin_bit, end_bit);
+        return GGD_E_INVALID;
+    }
+    const int num_passes = (end_bit - begin_bit + kRadixBits - 1) / kRadixBits;
+    const uint32_t cap = (uint32_t)capacity;
+    const uint32_t tiles = (uint32_t)((capacity + kSortTile - 1) / kSortTile);
+    if (tiles == 0) return GGD_OK;
+    if (!hist_precomputed) {
+        const int blocks = (int)std::min<uint64_t>((capacity + 255) / 256, 148 * 8);
+        histogram_kernel<<<blocks, 256, 0, s>>>(keys_in, n_dev, cap, begin_bit, end_bit, num_passes, sc.hist);
+        GGD_LAUNCH_CHECK("histogram_kernel");
+    }
+    const size_t lb_stride = (size_t)(tiles + 1) * kRadixBins;
+    for (int p = 0; p < num_passes; ++p) {
+        const int shift = begin_bit + p * kRadixBits;
+        const int bits = std::min(kRadixBits, end_bit - shift);
+        const uint32_t mask = (1u << bits) - 1u;
+        // the last pass lands in *_out; passes alternate backwards from there
+        const bool to_out = ((num_passes - 1 - p) % 2) == 0;
+        const uint64_t* kin = (p == 0) ? keys_in : (to_out ? keys_tmp : keys_out);
+        const uint32_t* vin = (p == 0) ? vals_in : (to_out ? vals_tmp : vals_out);
+        uint64_t* kout = to_out ? keys_out : keys_tmp;
+        uint32_t* vout = to_out ? vals_out : vals_tmp;
+        onesweep_kernel<<<tiles, kSortThreads, 0, s>>>(kin, kout, vin, vout, n_dev, cap, shift, mask,
+                                                       sc.hist + p * kRadixBins,
+                                                       sc.lookback + p * lb_stride, sc.tickets + p);
+        GGD_LAUNCH_CHECK("onesweep_kernel");
+    }
+    return GGD_OK;
+}
+
+int launch_duplicate(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g,
+                     const int* radii, const BinState& b, uint64_t capacity,
+                     const SortScratch& sc, int num_passes)
+{
+    const int blocks = (P + kDupThreads - 1) / kDupThreads;
+    duplicate_kernel<<<blocks, kDupThreads, 0, s>>>(P, grid_x, grid_y, g.means2D, g.depths,
+                                                    g.point_offsets, radii, b.keys_unsorted,
+                                                    b.vals_unsorted, (uint32_t)capacity, g.counters,
+                                                    sc.hist, num_passes);
+    GGD_LAUNCH_CHECK("duplicate_kernel");
+    return GGD_OK;
+}
+
+int launch_tile_ranges(cudaStream_t s, const GeomState& g, const BinState& b, uint64_t capacity,
+                       const ImgState& im, int tiles)
+{
+    (void)tiles;
+    const int blocks = (int)std::max<uint64_t>(1, std::min<uint64_t>((capacity + 255) / 256, 148 * 8));
+    tile_ranges_kernel<<<blocks, 256, 0, s>>>(g.counters + 3, b.keys, im.ranges);
+    GGD_LAUNCH_CHECK("tile_ranges_kernel");
+    return GGD_OK;
+}
+
+}  // namespace ggd

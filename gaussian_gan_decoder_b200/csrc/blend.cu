@@ -1,0 +1,113 @@
+// Stage 2b of the rasteriser: per-tile front-to-back alpha blending.
+//
+// Replaces FORWARD::render → renderCUDA (DGR/cuda_rasterizer/forward.cu:261-400).
+// One CTA per 16x16 tile, one thread per pixel.  The per-pixel arithmetic —
+// the falloff exponent, alpha = min(0.99, o·exp(power)), the 1/255 and 1e-4
+// tests, C += c·alpha·T, and the contributor bookkeeping — keeps the
+// reference's operation order exactly, because n_contrib (an integer output)
+// and the final T depend on every rounding along the way.
+//
+// What differs: a batch stages, per instance, the complete blend record
+// {xy, conic, opacity, rgb} in shared memory as two float4 + one float, so the
+// inner loop has no global loads at all (the reference gathers the colour from
+// global memory for every contributing (pixel, Gaussian) pair, forward.cu:355)
+// and every shared-memory read is a 16-byte broadcast.
+#include "common.cuh"
+
+namespace ggd {
+namespace {
+
+constexpr int kBatch = kTilePixels;  // 256 instances staged per round
+
+__global__ void __launch_bounds__(kTilePixels)
+blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+             const float2* __restrict__ means2D, const float* __restrict__ features,
+             const float4* __restrict__ conic_opacity, float* __restrict__ final_T,
+             uint32_t* __restrict__ n_contrib, const float* __restrict__ bg,
+             float* __restrict__ out_color)
+{
+    __shared__ float4 s_a[kBatch];  // x, y, conic.x, conic.y
+    __shared__ float4 s_b[kBatch];  // conic.z, opacity, r, g
+    __shared__ float s_c[kBatch];   // b
+
+    const uint32_t tiles_x = (W + kTileX - 1) / kTileX;
+    const uint32_t px = blockIdx.x * kTileX + threadIdx.x;
+    const uint32_t py = blockIdx.y * kTileY + threadIdx.y;
+    const uint32_t pix_id = W * py + px;
+    const float fx = (float)px, fy = (float)py;
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    bool done = !inside;
+    const int tr = threadIdx.y * kTileX + threadIdx.x;
+
+    const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
+    const int rounds = (int)((range.y - range.x + kBatch - 1) / kBatch);
+    int to_do = (int)(range.y - range.x);
+
+    float T = 1.0f;
+    uint32_t contributor = 0, last_contributor = 0;
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+
+    for (int i = 0; i < rounds; ++i, to_do -= kBatch) {
+        if (__syncthreads_count(done) == kTilePixels) break;
+        const uint32_t progress = (uint32_t)i * kBatch + tr;
+        if (range.x + progress < range.y) {
+            const uint32_t id = __ldg(point_list + range.x + progress);
+            const float2 xy = __ldg(means2D + id);
+            const float4 co = __ldg(conic_opacity + id);
+            const float r = __ldg(features + 3 * (size_t)id);
+            const float g = __ldg(features + 3 * (size_t)id + 1);
+            const float b = __ldg(features + 3 * (size_t)id + 2);
+            s_a[tr] = make_float4(xy.x, xy.y, co.x, co.y);
+            s_b[tr] = make_float4(co.z, co.w, r, g);
+            s_c[tr] = b;
+        }
+        __syncthreads();
+
+        const int lim = min(kBatch, to_do);
+        for (int j = 0; !done && j < lim; ++j) {
+            contributor++;
+            const float4 A = s_a[j];
+            const float4 B = s_b[j];
+            const float dx = A.x - fx, dy = A.y - fy;
+            const float power = -0.5f * (A.z * dx * dx + B.x * dy * dy) - A.w * dx * dy;
+            if (power > 0.0f) continue;
+            const float alpha = min(0.99f, B.y * expf(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) {
+                done = true;
+                continue;
+            }
+            C0 += B.z * alpha * T;
+            C1 += B.w * alpha * T;
+            C2 += s_c[j] * alpha * T;
+            T = test_T;
+            last_contributor = contributor;
+        }
+    }
+
+    if (inside) {
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+        const size_t plane = (size_t)H * W;
+        out_color[pix_id] = C0 + T * bg[0];
+        out_color[plane + pix_id] = C1 + T * bg[1];
+        out_color[2 * plane + pix_id] = C2 + T * bg[2];
+    }
+}
+
+}  // namespace
+
+int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const GeomState& g,
+                 const BinState& b, const ImgState& im, const float* features,
+                 const float* background, float* out_color)
+{
+    dim3 grid(grid_x, grid_y, 1), block(kTileX, kTileY, 1);
+    blend_kernel<<<grid, block, 0, s>>>(im.ranges, b.vals, W, H, g.means2D, features,
+                                        g.conic_opacity, im.accum_alpha, im.n_contrib, background,
+                                        out_color);
+    GGD_LAUNCH_CHECK("blend_kernel");
+    return GGD_OK;
+}
+
+}  // namespace ggd

@@ -1,0 +1,146 @@
+/*
+ * ggd.h — C ABI of the B200-native (sm_100a) decode → rasterise hot path.
+ *
+ * Every entry point takes plain pointers and sizes; device pointers are raw
+ * CUDA device addresses, `stream` is a cudaStream_t passed as void*.  No torch
+ * type crosses this boundary.  All functions return 0 on success and a
+ * non-zero GGD_E_* code otherwise; ggd_last_error() returns a thread-local,
+ * human-readable message for the last failure.  Nothing here allocates device
+ * memory: the caller owns every buffer (the Python host side uses torch uint8
+ * tensors so ownership matches the reference, whose three state buffers are
+ * torch tensors returned to Python, DGR/rasterize_points.cu:68-78).
+ *
+ * Citations are into /root/reference; DGR abbreviates
+ * gaussian_splatting/submodules/diff-gaussian-rasterization.
+ */
+#ifndef GGD_H_INCLUDED
+#define GGD_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GGD_API __attribute__((visibility("default")))
+#else
+#define GGD_API
+#endif
+
+#define GGD_OK 0
+#define GGD_E_INVALID 1   /* bad argument / unsupported combination            */
+#define GGD_E_CUDA 2      /* a CUDA runtime call or kernel launch failed        */
+#define GGD_E_CAPACITY 3  /* a caller-provided buffer is too small              */
+
+/* Tile size of the rasteriser. Part of the bit-exact contract: tile keys and
+ * ranges depend on it (DGR/cuda_rasterizer/config.h:16-17). */
+#define GGD_TILE_X 16
+#define GGD_TILE_Y 16
+
+GGD_API const char* ggd_last_error(void);
+/* ABI version of this header; bumped on any signature change. */
+GGD_API int ggd_abi_version(void);
+
+/* ------------------------------------------------------------------------ */
+/* Rasteriser forward                                                        */
+/* ------------------------------------------------------------------------ */
+
+/* Bytes required for the three state buffers.  Replaces
+ * CudaRasterizer::required<GeometryState|BinningState|ImageState>
+ * (DGR/cuda_rasterizer/rasterizer_impl.h:66-72) and the fromChunk layouts
+ * (rasterizer_impl.cu:155-194).  `bin_capacity` is the number of
+ * (Gaussian, tile) instances the binning buffer can hold; unlike the
+ * reference the binning buffer is sized BEFORE the frame runs, which is what
+ * removes the reference's mid-frame device→host sync (rasterizer_impl.cu:281).
+ * sizes_out = { geom_bytes, binning_bytes, img_bytes }. */
+GGD_API int ggd_raster_workspace_sizes(int P, int W, int H, uint64_t bin_capacity, size_t sizes_out[3]);
+
+/* Stage 1: per-Gaussian projection, covariance, SH→RGB, culling, tile rects,
+ * then the inclusive prefix sum of tiles_touched.  Replaces
+ * FORWARD::preprocess → preprocessCUDA (DGR/cuda_rasterizer/forward.cu:155-256,
+ * :402-455) and cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:277).
+ * Pointer arguments follow CudaRasterizer::Rasterizer::forward
+ * (DGR/cuda_rasterizer/rasterizer.h:31-54): exactly one of shs /
+ * colors_precomp and exactly one of (scales, rotations) / cov3D_precomp is
+ * non-NULL.  `radii` may be NULL (an internal array is used).
+ * `num_rendered_host`, if non-NULL, receives the instance count R through an
+ * asynchronous device→host copy on `stream` (valid after the stream is
+ * synchronised; use pinned memory to keep the copy asynchronous). */
+GGD_API int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int H,
+                          const float* means3D, const float* shs, const float* colors_precomp,
+                          const float* opacities, const float* scales, float scale_modifier,
+                          const float* rotations, const float* cov3D_precomp,
+                          const float* viewmatrix, const float* projmatrix, const float* campos,
+                          float tan_fovx, float tan_fovy, int prefiltered,
+                          void* geom_ws, int* radii, uint32_t* num_rendered_host);
+
+/* Stage 2: key duplication, radix sort, tile ranges, blending.  Replaces
+ * duplicateWithKeys (rasterizer_impl.cu:70-111), getHigherMsb (:35-50),
+ * cub::DeviceRadixSort::SortPairs (:303-308), the ranges memset +
+ * identifyTileRanges (:116-138, :310-318) and FORWARD::render → renderCUDA
+ * (forward.cu:261-400).  R is read from geom_ws ON THE DEVICE; if R exceeds
+ * bin_capacity nothing past the capacity is written, the overflow flag in
+ * geom_ws is raised (see ggd_raster_status) and the image is undefined — the
+ * caller re-runs this stage with a larger binning buffer. */
+GGD_API int ggd_raster_render(void* stream, int P, int W, int H, const float* background,
+                      const float* colors_precomp, const int* radii,
+                      void* geom_ws, void* bin_ws, uint64_t bin_capacity, void* img_ws,
+                      float* out_color);
+
+/* Stages 1+2 back to back on `stream`, no host synchronisation.  Replaces
+ * CudaRasterizer::Rasterizer::forward (rasterizer_impl.cu:198-337). */
+GGD_API int ggd_raster_forward(void* stream, int P, int D, int M, const float* background, int W, int H,
+                       const float* means3D, const float* shs, const float* colors_precomp,
+                       const float* opacities, const float* scales, float scale_modifier,
+                       const float* rotations, const float* cov3D_precomp,
+                       const float* viewmatrix, const float* projmatrix, const float* campos,
+                       float tan_fovx, float tan_fovy, int prefiltered,
+                       void* geom_ws, void* bin_ws, uint64_t bin_capacity, void* img_ws,
+                       float* out_color, int* radii, uint32_t* num_rendered_host);
+
+/* Blocking read-back of { num_rendered, overflow_flag } from geom_ws
+ * (synchronises `stream`).  The reference returns num_rendered from forward
+ * (rasterizer_impl.cu:336); here it is a separate, optional query. */
+GGD_API int ggd_raster_status(void* stream, const void* geom_ws, int P, uint32_t out[2]);
+
+/* Frustum test only.  Replaces Rasterizer::markVisible → checkFrustum
+ * (rasterizer_impl.cu:54-66, :141-152).  `present` is P bytes (bool). */
+GGD_API int ggd_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present);
+
+/* Field locator for tests/debugging: byte offset and element count of a named
+ * array inside a state buffer.  The reference exposes its layout only through
+ * fromChunk (rasterizer_impl.cu:155-194).  which: 0 geom, 1 binning, 2 img.
+ * geom: "depths" f32[P], "radii" i32[P], "means2D" f32[2P], "cov3D" f32[6P],
+ *       "conic_opacity" f32[4P], "rgb" f32[3P], "tiles_touched" u32[P],
+ *       "point_offsets" u32[P], "clamped" u8[3P], "num_rendered" u32[2]
+ * binning (needs R = num_rendered ≤ capacity): "point_list" u32[R],
+ *       "point_list_unsorted" u32[R], "point_list_keys" u64[R],
+ *       "point_list_keys_unsorted" u64[R]
+ * img:  "accum_alpha" f32[WH], "n_contrib" u32[WH], "ranges" u32[2*tiles] */
+GGD_API int ggd_raster_field(int which, const char* name, int P, int W, int H, uint64_t bin_capacity,
+                     size_t* byte_offset, size_t* count);
+
+/* ------------------------------------------------------------------------ */
+/* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs           */
+/* ------------------------------------------------------------------------ */
+
+/* Replaces the reference's call into cub::DeviceRadixSort::SortPairs
+ * (CUB of CUDA 12.x, not vendored; call site rasterizer_impl.cu:303-308):
+ * stable sort on key bits [begin_bit, end_bit).  `n_dev` points to the element
+ * count in DEVICE memory (so it can be produced by an earlier kernel without a
+ * host sync); `capacity` bounds it.  keys_in/vals_in are preserved; the sorted
+ * result is written to keys_out/vals_out.  `scratch` must hold
+ * ggd_sort_scratch_bytes(capacity) bytes. */
+GGD_API size_t ggd_sort_scratch_bytes(uint64_t capacity);
+GGD_API int ggd_sort_pairs(void* stream, const uint64_t* keys_in, uint64_t* keys_out,
+                   const uint32_t* vals_in, uint32_t* vals_out,
+                   const uint32_t* n_dev, uint64_t capacity, int begin_bit, int end_bit,
+                   uint64_t* keys_tmp, uint32_t* vals_tmp, void* scratch, size_t scratch_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGD_H_INCLUDED */
