@@ -68,19 +68,23 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
             contributor++;
             const float4 A = s_a[j];
             const float4 B = s_b[j];
-            const float dx = A.x - fx, dy = A.y - fy;
-            const float power = -0.5f * (A.z * dx * dx + B.x * dy * dy) - A.w * dx * dy;
+            // Every product/sum below is pinned (_rn intrinsics are never re-fused by ptxas) to
+            // the FMA placement of the reference build: q = fma(dx, cx*dx, cz*dy*dy),
+            // power = fma(q, -0.5, -(cy*dx*dy)), C = fma(T, alpha*c, C).
+            const float dx = __fsub_rn(A.x, fx), dy = __fsub_rn(A.y, fy);
+            const float q = __fmaf_rn(dx, __fmul_rn(dx, A.z), __fmul_rn(dy, __fmul_rn(dy, B.x)));
+            const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, A.w)));
             if (power > 0.0f) continue;
-            const float alpha = min(0.99f, B.y * expf(power));
+            const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
             if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1 - alpha);
+            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
             if (test_T < 0.0001f) {
                 done = true;
                 continue;
             }
-            C0 += B.z * alpha * T;
-            C1 += B.w * alpha * T;
-            C2 += s_c[j] * alpha * T;
+            C0 = __fmaf_rn(T, __fmul_rn(alpha, B.z), C0);
+            C1 = __fmaf_rn(T, __fmul_rn(alpha, B.w), C1);
+            C2 = __fmaf_rn(T, __fmul_rn(alpha, s_c[j]), C2);
             T = test_T;
             last_contributor = contributor;
         }
@@ -90,9 +94,9 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
         final_T[pix_id] = T;
         n_contrib[pix_id] = last_contributor;
         const size_t plane = (size_t)H * W;
-        out_color[pix_id] = C0 + T * bg[0];
-        out_color[plane + pix_id] = C1 + T * bg[1];
-        out_color[2 * plane + pix_id] = C2 + T * bg[2];
+        out_color[pix_id] = __fmaf_rn(T, bg[0], C0);
+        out_color[plane + pix_id] = __fmaf_rn(T, bg[1], C1);
+        out_color[2 * plane + pix_id] = __fmaf_rn(T, bg[2], C2);
     }
 }
 

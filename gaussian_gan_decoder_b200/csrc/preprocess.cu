@@ -199,9 +199,21 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
                 S.m[0][0] = a.scale_modifier * s_cov[3 * t];
                 S.m[1][1] = a.scale_modifier * s_cov[3 * t + 1];
                 S.m[2][2] = a.scale_modifier * s_cov[3 * t + 2];
-                const M3 R = {{{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
-                               {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
-                               {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}}};
+                // The nine rotation entries share products (x*y, r*z, ...).  For shared products
+                // the compiler leaves mul/add pairs unfused in PTX and ptxas then picks which
+                // product to fold into an FFMA; that choice is context dependent, so it is
+                // pinned here to what the reference build does (read from its SASS): the
+                // r-product is the rounded addend for xy/yz, the xz product for the xz pair.
+                const float xz = __fmul_rn(x, z), rx = __fmul_rn(r, x), rz = __fmul_rn(r, z);
+                const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+                const float xy_m_rz = __fmaf_rn(x, y, -rz), xy_p_rz = __fmaf_rn(x, y, rz);
+                const float xz_p_ry = __fmaf_rn(r, y, xz), xz_m_ry = __fmaf_rn(-r, y, xz);
+                const float yz_m_rx = __fmaf_rn(y, z, -rx), yz_p_rx = __fmaf_rn(y, z, rx);
+                const float yy_p_zz = __fadd_rn(yy, zz);
+                const float xx_p_zz = __fmaf_rn(x, x, zz), xx_p_yy = __fmaf_rn(x, x, yy);
+                const M3 R = {{{1.f - 2.f * yy_p_zz, 2.f * xy_m_rz, 2.f * xz_p_ry},
+                               {2.f * xy_p_rz, 1.f - 2.f * xx_p_zz, 2.f * yz_m_rx},
+                               {2.f * xz_m_ry, 2.f * yz_p_rx, 1.f - 2.f * xx_p_yy}}};
                 const M3 Mm = mul(S, R);
                 const M3 Sig = mul(transpose(Mm), Mm);
                 cov6[0] = Sig.m[0][0]; cov6[1] = Sig.m[0][1]; cov6[2] = Sig.m[0][2];
@@ -229,13 +241,16 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
             c2.m[1][1] += 0.3f;
             const float cx = c2.m[0][0], cy = c2.m[0][1], cz = c2.m[1][1];
 
-            const float det = (cx * cz - cy * cy);
+            // same pinning as above: det = fma(cx, cz, -(cy*cy)), disc = fma(mid, mid, -det),
+            // lambda = mid +- sqrt(disc) with mid rounded (reference SASS, forward.cu:216-230)
+            const float det = __fmaf_rn(cx, cz, -__fmul_rn(cy, cy));
             if (det != 0.0f) {
                 const float det_inv = 1.f / det;
                 const float3 conic = make_float3(cz * det_inv, -cy * det_inv, cx * det_inv);
-                const float mid = 0.5f * (cx + cz);
-                const float lambda1 = mid + sqrtf(max(0.1f, mid * mid - det));
-                const float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
+                const float mid = __fmul_rn(0.5f, __fadd_rn(cx, cz));
+                const float disc = sqrtf(max(0.1f, __fmaf_rn(mid, mid, -det)));
+                const float lambda1 = __fadd_rn(mid, disc);
+                const float lambda2 = __fsub_rn(mid, disc);
                 const float my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
                 const float2 pix = make_float2(ndc_to_pix(proj.x, a.W), ndc_to_pix(proj.y, a.H));
                 uint2 rmin, rmax;
