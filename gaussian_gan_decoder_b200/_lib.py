@@ -27,6 +27,17 @@ _i = C.c_int
 _u64 = C.c_uint64
 _sz = C.c_size_t
 
+
+
+class DecoderConfig(C.Structure):
+    """ctypes mirror of ``ggd_decoder_config`` (include/ggd.h)."""
+    _fields_ = [("arch", C.c_int), ("variant", C.c_int), ("plane_depth", C.c_int), ("plane_h", C.c_int),
+                ("plane_w", C.c_int), ("pos_freqs", C.c_int), ("hidden", C.c_int), ("box_warp", C.c_float),
+                ("scale_bias", C.c_float)]
+
+
+_cfg = C.POINTER(DecoderConfig)
+
 # name -> (restype, argtypes); mirrors include/ggd.h declaration by declaration
 SIGNATURES = {
     "ggd_last_error": (C.c_char_p, []),
@@ -40,8 +51,15 @@ SIGNATURES = {
     "ggd_raster_status": (_i, [_p, _p, _i, C.POINTER(C.c_uint32)]),
     "ggd_mark_visible": (_i, [_p, _i, _p, _p, _p, _p]),
     "ggd_raster_field": (_i, [_i, C.c_char_p, _i, _i, _i, _u64, C.POINTER(_sz), C.POINTER(_sz)]),
+    "ggd_stage_timing": (_i, [_i]),
+    "ggd_stage_times": (_i, [C.POINTER(C.c_float)]),
     "ggd_sort_scratch_bytes": (_sz, [_u64]),
     "ggd_sort_pairs": (_i, [_p, _p, _p, _p, _p, _p, _u64, _i, _i, _p, _p, _p, _sz]),
+    "ggd_decode_param_counts": (_i, [_cfg, C.POINTER(_sz), C.POINTER(_sz)]),
+    "ggd_decode_param_offset": (_i, [_cfg, _i, _i, _i, C.POINTER(_sz), C.POINTER(_i), C.POINTER(_i)]),
+    "ggd_decode_pack_weights": (_i, [_p, _cfg, _p, _p]),
+    "ggd_planes_channels_last": (_i, [_p, _cfg, _p, _p]),
+    "ggd_decode_forward": (_i, [_p, _cfg, _p, _p, _i, _p] + [_p] * 8),
 }
 
 _lib = None

@@ -17,6 +17,22 @@ void set_error(const char* fmt, ...)
     va_end(ap);
 }
 
+// ---- stage timing ---------------------------------------------------------
+static bool g_timing = false;
+static cudaEvent_t g_ev[kStCount][2];
+static bool g_ev_made = false, g_ev_used[kStCount];
+
+void stage_mark(cudaStream_t s, int stage, bool begin)
+{
+    if (!g_timing) return;
+    if (!g_ev_made) {
+        for (int i = 0; i < kStCount; ++i) { cudaEventCreate(&g_ev[i][0]); cudaEventCreate(&g_ev[i][1]); g_ev_used[i] = false; }
+        g_ev_made = true;
+    }
+    cudaEventRecord(g_ev[stage][begin ? 0 : 1], s);
+    if (!begin) g_ev_used[stage] = true;
+}
+
 namespace {
 template <typename T>
 T* take(char*& p, size_t count)
@@ -148,8 +164,8 @@ int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int H,
 
     const size_t zero = (size_t)(reinterpret_cast<char*>(geom_ws) + g.bytes - reinterpret_cast<char*>(g.counters));
     GGD_CUDA_CHECK(cudaMemsetAsync(g.counters, 0, zero, s));
-    if (int e = launch_preprocess(s, a, g, radii)) return e;
-    if (int e = launch_scan(s, P, g)) return e;
+    { StageScope t(s, kStPreprocess); if (int e = launch_preprocess(s, a, g, radii)) return e; }
+    { StageScope t(s, kStScan); if (int e = launch_scan(s, P, g)) return e; }
     if (num_rendered_host)
         GGD_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, g.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     return GGD_OK;
@@ -178,13 +194,15 @@ int ggd_raster_render(void* stream, int P, int W, int H, const float* background
     SortScratch sc = carve_sort_scratch(b.sort_scratch, bin_capacity);
     GGD_CUDA_CHECK(cudaMemsetAsync(b.sort_scratch, 0, sc.zero_bytes, s));
     GGD_CUDA_CHECK(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)tiles, s));
-    if (int e = launch_duplicate(s, P, grid_x, grid_y, g, radii, b, bin_capacity, sc, num_passes)) return e;
+    { StageScope t(s, kStDuplicate); if (int e = launch_duplicate(s, P, grid_x, grid_y, g, radii, b, bin_capacity, sc, num_passes)) return e; }
     if (bin_capacity > 0) {
-        if (int e = sort_pairs(s, b.keys_unsorted, b.keys, b.vals_unsorted, b.vals, g.counters + 3,
-                               bin_capacity, 0, end_bit, b.keys_tmp, b.vals_tmp, sc, true)) return e;
-        if (int e = launch_tile_ranges(s, g, b, bin_capacity, im, tiles)) return e;
+        { StageScope t(s, kStSort);
+          if (int e = sort_pairs(s, b.keys_unsorted, b.keys, b.vals_unsorted, b.vals, g.counters + 3,
+                                 bin_capacity, 0, end_bit, b.keys_tmp, b.vals_tmp, sc, true)) return e; }
+        { StageScope t(s, kStRanges); if (int e = launch_tile_ranges(s, g, b, bin_capacity, im, tiles)) return e; }
     }
     const float* features = colors_precomp ? colors_precomp : g.rgb;
+    StageScope t(s, kStBlend);
     return launch_blend(s, W, H, grid_x, grid_y, g, b, im, features, background, out_color);
 }
 
@@ -254,6 +272,21 @@ int ggd_raster_field(int which, const char* name, int P, int W, int H, uint64_t 
     }
     set_error("ggd_raster_field: unknown field %d/%s", which, name);
     return GGD_E_INVALID;
+}
+
+int ggd_stage_timing(int enable) { g_timing = enable != 0; return GGD_OK; }
+
+int ggd_stage_times(float ms_out[8])
+{
+    if (!ms_out) { set_error("ggd_stage_times: null pointer"); return GGD_E_INVALID; }
+    for (int i = 0; i < kStCount; ++i) {
+        ms_out[i] = -1.f;
+        if (g_ev_made && g_ev_used[i]) {
+            GGD_CUDA_CHECK(cudaEventSynchronize(g_ev[i][1]));
+            GGD_CUDA_CHECK(cudaEventElapsedTime(&ms_out[i], g_ev[i][0], g_ev[i][1]));
+        }
+    }
+    return GGD_OK;
 }
 
 size_t ggd_sort_scratch_bytes(uint64_t capacity) { return carve_sort_scratch(nullptr, capacity).bytes; }

@@ -1,0 +1,91 @@
+// extern "C" entry points of the decoder half (include/ggd.h).
+#include "decode.cuh"
+
+namespace ggd {
+
+int launch_pack_weights(cudaStream_t s, const DecoderLayout& L, const float* flat, float* packed);
+int launch_planes_channels_last(cudaStream_t s, const float* src, float* dst, int D, int H, int W);
+}  // namespace ggd
+#include "decode_args.cuh"
+
+using namespace ggd;
+
+namespace {
+int check_cfg(const ggd_decoder_config* c, DecoderLayout* L)
+{
+    if (!c) { set_error("null decoder config"); return GGD_E_INVALID; }
+    if (c->hidden != kHidden) { set_error("hidden_dim %d unsupported: kernels are specialised for %d", c->hidden, kHidden); return GGD_E_INVALID; }
+    if (c->arch != 0 && c->arch != 1) { set_error("arch must be 0 (eg3d) or 1 (panohead)"); return GGD_E_INVALID; }
+    if (c->plane_depth < 1 || (c->arch == 0 && c->plane_depth != 1)) { set_error("bad plane_depth %d for arch %d", c->plane_depth, c->arch); return GGD_E_INVALID; }
+    if (c->plane_h < 1 || c->plane_w < 1 || !(c->box_warp > 0.f)) { set_error("bad plane size / box_warp"); return GGD_E_INVALID; }
+    if (!make_decoder_layout(c->variant, c->pos_freqs, L)) { set_error("unsupported decoder variant %d / pos_freqs %d", c->variant, c->pos_freqs); return GGD_E_INVALID; }
+    return GGD_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ggd_decode_param_counts(const ggd_decoder_config* cfg, size_t* flat_floats, size_t* packed_floats)
+{
+    DecoderLayout L;
+    if (int e = check_cfg(cfg, &L)) return e;
+    if (flat_floats) *flat_floats = L.flat_count;
+    if (packed_floats) *packed_floats = L.pk_count;
+    return GGD_OK;
+}
+
+int ggd_decode_param_offset(const ggd_decoder_config* cfg, int head, int layer, int is_bias,
+                            size_t* offset, int* fan_in, int* fan_out)
+{
+    DecoderLayout L;
+    if (int e = check_cfg(cfg, &L)) return e;
+    if (head < 0 || head >= kHeads || layer < 0 || layer >= kLayers || !offset) { set_error("bad head/layer"); return GGD_E_INVALID; }
+    *offset = is_bias ? L.flat_b[head][layer] : L.flat_w[head][layer];
+    if (fan_in) *fan_in = layer == 0 ? L.in_dim[head] : kHidden;
+    if (fan_out) *fan_out = layer == kLayers - 1 ? head_out(head) : kHidden;
+    return GGD_OK;
+}
+
+int ggd_decode_pack_weights(void* stream, const ggd_decoder_config* cfg, const float* flat_params, float* packed)
+{
+    DecoderLayout L;
+    if (int e = check_cfg(cfg, &L)) return e;
+    if (!flat_params || !packed) { set_error("ggd_decode_pack_weights: null pointer"); return GGD_E_INVALID; }
+    return launch_pack_weights(static_cast<cudaStream_t>(stream), L, flat_params, packed);
+}
+
+int ggd_planes_channels_last(void* stream, const ggd_decoder_config* cfg, const float* planes_nchw, float* planes_cl)
+{
+    DecoderLayout L;
+    if (int e = check_cfg(cfg, &L)) return e;
+    if (!planes_nchw || !planes_cl) { set_error("ggd_planes_channels_last: null pointer"); return GGD_E_INVALID; }
+    StageScope t(static_cast<cudaStream_t>(stream), kStPlanes);
+    return launch_planes_channels_last(static_cast<cudaStream_t>(stream), planes_nchw, planes_cl,
+                                       cfg->plane_depth, cfg->plane_h, cfg->plane_w);
+}
+
+int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl,
+                       const float* xyz, int P, const float* packed,
+                       float* out_xyz, float* out_scale, float* out_rotation,
+                       float* out_opacity, float* out_color,
+                       float* act_scale, float* act_rotation, float* act_opacity)
+{
+    DecodeFwdArgs a;
+    if (int e = check_cfg(cfg, &a.L)) return e;
+    if (P <= 0) { set_error("P must be positive (got %d)", P); return GGD_E_INVALID; }
+    if (!planes_cl || !xyz || !packed || !out_xyz || !out_scale || !out_rotation || !out_opacity || !out_color) { set_error("ggd_decode_forward: null required pointer"); return GGD_E_INVALID; }
+    if ((reinterpret_cast<uintptr_t>(planes_cl) & 15) || (reinterpret_cast<uintptr_t>(packed) & 15)) { set_error("planes_cl and packed must be 16-byte aligned"); return GGD_E_INVALID; }
+    a.planes = planes_cl; a.arch = cfg->arch; a.D = cfg->plane_depth; a.H = cfg->plane_h; a.W = cfg->plane_w;
+    a.coord_scale = 2.0f / cfg->box_warp; a.pos_freqs = cfg->pos_freqs; a.scale_bias = cfg->scale_bias;
+    a.xyz = xyz; a.P = P; a.packed = packed;
+    a.out[kXyz] = out_xyz; a.out[kScale] = out_scale; a.out[kRot] = out_rotation;
+    a.out[kOpacity] = out_opacity; a.out[kColor] = out_color;
+    a.act_scale = act_scale; a.act_rot = act_rotation; a.act_opacity = act_opacity;
+    int dev = 0, sms = 0;
+    GGD_CUDA_CHECK(cudaGetDevice(&dev));
+    GGD_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    StageScope t(static_cast<cudaStream_t>(stream), kStDecode);
+    return launch_decode_fwd(static_cast<cudaStream_t>(stream), a, sms);
+}
+
+}  // extern "C"

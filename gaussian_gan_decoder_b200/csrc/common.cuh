@@ -28,6 +28,15 @@ void set_error(const char* fmt, ...);
         }                                                                             \
     } while (0)
 
+// ---- optional per-stage device timing (ggd_stage_timing / ggd_stage_times) ----
+enum Stage { kStPlanes = 0, kStDecode, kStPreprocess, kStScan, kStDuplicate, kStSort, kStRanges, kStBlend, kStCount };
+void stage_mark(cudaStream_t s, int stage, bool begin);   // no-op unless timing is enabled
+struct StageScope {
+    cudaStream_t s; int st;
+    StageScope(cudaStream_t s_, int st_) : s(s_), st(st_) { stage_mark(s, st, true); }
+    ~StageScope() { stage_mark(s, st, false); }
+};
+
 constexpr int kTileX = GGD_TILE_X;
 constexpr int kTileY = GGD_TILE_Y;
 constexpr int kTilePixels = kTileX * kTileY;

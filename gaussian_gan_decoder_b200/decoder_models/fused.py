@@ -1,0 +1,150 @@
+"""Host side of the fused sample+decode kernel: flat parameter storage, config
+marshalling and the autograd boundary.  Everything numeric happens in
+``libggd_b200.so`` (ggd_decode_* in include/ggd.h).
+"""
+import ctypes as C
+
+import torch
+
+from .. import _lib
+
+HEADS = ("xyz", "scale", "rotation", "opacity", "color")     # get_params_custom() order
+VARIANTS = {"parallel": 0, "sequential": 1, "sequential_reverse": 2}
+ARCHS = {"eg3d": 0, "panohead": 1}
+
+
+DecoderConfig = _lib.DecoderConfig
+
+
+def _bind(lib):
+    """signatures are bound by _lib.load()"""
+
+
+def make_config(arch, variant, depth, h, w, pos_freqs, hidden, box_warp, scale_bias):
+    return DecoderConfig(ARCHS[arch], VARIANTS[variant], int(depth), int(h), int(w), int(pos_freqs), int(hidden),
+                         float(box_warp), float(scale_bias))
+
+
+def param_counts(cfg):
+    lib = _lib.load(); _bind(lib)
+    a, b = C.c_size_t(), C.c_size_t()
+    _lib.check(lib.ggd_decode_param_counts(C.byref(cfg), C.byref(a), C.byref(b)))
+    return a.value, b.value
+
+
+def param_offset(cfg, head, layer, is_bias):
+    lib = _lib.load(); _bind(lib)
+    off, fi, fo = C.c_size_t(), C.c_int(), C.c_int()
+    _lib.check(lib.ggd_decode_param_offset(C.byref(cfg), head, layer, int(is_bias), C.byref(off), C.byref(fi), C.byref(fo)))
+    return off.value, fi.value, fo.value
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class FlatParams:
+    """One contiguous fp32 buffer holding all 40 decoder tensors in the ggd.h layout; the
+    nn.Linear parameters are re-pointed to views of it, so the optimizer updates the buffer
+    in place and a data-parallel job all-reduces ONE gradient buffer."""
+
+    def __init__(self, owner, cfg):
+        self.cfg = cfg
+        self.count, self.packed_count = param_counts(cfg)
+        self.flat = None
+        self.flat_grad = None
+        self.packed = None
+        self._packed_version = None
+        self.adopt(owner)
+
+    def _tensors(self, owner):
+        for hi, h in enumerate(HEADS):
+            for li, lin in enumerate(getattr(owner, f"{h}_decoder").linears()):
+                yield hi, li, 0, lin.weight
+                yield hi, li, 1, lin.bias
+
+    def adopt(self, owner):
+        first = next(self._tensors(owner))[3]
+        dev = first.device
+        flat = torch.empty(self.count, dtype=torch.float32, device=dev)
+        grad = torch.zeros(self.count, dtype=torch.float32, device=dev)
+        with torch.no_grad():
+            for hi, li, is_b, t in self._tensors(owner):
+                off, fi, fo = param_offset(self.cfg, hi, li, is_b)
+                shape = (fo,) if is_b else (fo, fi)
+                if tuple(t.shape) != shape:
+                    raise ValueError(f"{HEADS[hi]}_decoder layer {li}: expected {shape}, got {tuple(t.shape)}")
+                view = flat[off:off + t.numel()].view(shape)
+                view.copy_(t.detach().to(torch.float32))
+                t.data = view
+                t.grad = grad[off:off + t.numel()].view(shape)
+        self.flat, self.flat_grad = flat, grad
+        self._packed_version = None
+
+    def in_sync(self, owner):
+        first = next(self._tensors(owner))[3]
+        return self.flat is not None and first.data_ptr() == self.flat.data_ptr() and first.device == self.flat.device
+
+    def packed_weights(self):
+        """Kernel-layout copy of the parameters, rebuilt only when the flat buffer changed."""
+        ver = self.flat._version
+        if self.packed is None or self.packed.device != self.flat.device or self._packed_version != ver:
+            lib = _lib.load(); _bind(lib)
+            if self.packed is None or self.packed.device != self.flat.device:
+                self.packed = torch.empty(self.packed_count, dtype=torch.float32, device=self.flat.device)
+            with torch.cuda.device(self.flat.device):
+                _lib.check(lib.ggd_decode_pack_weights(_stream(), C.byref(self.cfg), _lib.ptr(self.flat), _lib.ptr(self.packed)))
+            self._packed_version = ver
+        return self.packed
+
+
+def decode_forward(cfg, planes_nchw, xyz, packed, with_activations=True):
+    """planes [1,3,32*D,H,W] fp32 (generator layout), xyz [P,3] -> dict of raw attributes
+    (+ activated scale/rotation/opacity for the rasteriser)."""
+    lib = _lib.load(); _bind(lib)
+    if not xyz.is_cuda:
+        raise RuntimeError("init_position must be a CUDA tensor: the decoder has no CPU path")
+    dev = xyz.device
+    P = xyz.shape[0]
+    if planes_nchw.dim() != 5 or planes_nchw.shape[0] != 1 or planes_nchw.shape[1] != 3:
+        raise ValueError(f"feature_planes must be [1,3,C*D,H,W], got {tuple(planes_nchw.shape)}")
+    planes_nchw = planes_nchw.to(device=dev, dtype=torch.float32).contiguous()
+    xyz = xyz.to(torch.float32).contiguous()
+    new = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+    out = dict(xyz=new(P, 3), scale=new(P, 3), rotation=new(P, 4), opacity=new(P, 1), color=new(P, 3))
+    act = dict(act_scale=new(P, 3), act_rotation=new(P, 4), act_opacity=new(P, 1)) if with_activations else {}
+    if P == 0:
+        return {**out, **act}
+    p = _lib.ptr
+    with torch.cuda.device(dev):
+        s = _stream()
+        planes_cl = torch.empty(planes_nchw.numel(), dtype=torch.float32, device=dev)
+        _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(planes_cl)))
+        _lib.check(lib.ggd_decode_forward(s, C.byref(cfg), p(planes_cl), p(xyz), P, p(packed),
+                                          p(out["xyz"]), p(out["scale"]), p(out["rotation"]), p(out["opacity"]),
+                                          p(out["color"]), p(act.get("act_scale")), p(act.get("act_rotation")),
+                                          p(act.get("act_opacity"))))
+    return {**out, **act}
+
+
+class _FusedDecode(torch.autograd.Function):
+    """Autograd boundary of the fused kernel.  Inputs that can require grad: the flat
+    parameter buffer and the feature planes (use_gen_finetune)."""
+
+    @staticmethod
+    def forward(ctx, owner, planes, xyz, flat):
+        res = decode_forward(owner._cfg_for(planes), planes, xyz, owner._flat.packed_weights())
+        owner._last_activated = {k: res[k] for k in ("act_scale", "act_rotation", "act_opacity")}
+        ctx.owner = owner
+        ctx.save_for_backward(planes, xyz)
+        return res["xyz"], res["scale"], res["rotation"], res["opacity"], res["color"]
+
+    @staticmethod
+    def backward(ctx, *grads):
+        from . import fused_backward
+        return fused_backward.backward(ctx, *grads)
+
+
+def single_head_forward(decoder, triplane_features, gaussian_features):
+    from . import fused_single
+    return fused_single.forward(decoder, triplane_features, gaussian_features)

@@ -1,0 +1,76 @@
+"""Sync-free decode -> rasterise frame loop over pre-allocated buffers.
+
+This is the "N1" caller shape of SURVEY §8(f): what the reference's demo / viewer loop
+(main/load_decoder.py:12-25: decoder(...) -> GaussianModel -> CustomCam -> render_simple)
+does per frame, but with every buffer allocated once and no host synchronisation inside a
+frame.  It talks to ``libggd_b200.so`` directly; results are identical to going through the
+decoder classes + ``render_simple`` (tests/test_pipeline_gpu.py).
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib, rasterizer
+from .decoder_models import fused
+
+
+class FramePipeline:
+    def __init__(self, decoder, P, size, device, capacity=None):
+        self.lib = _lib.load()
+        self.dec = decoder
+        self.P, self.W, self.H = int(P), int(size), int(size)
+        self.dev = torch.device(device)
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        self.out = {k: torch.empty(P, n, **f32) for k, n in
+                    (("xyz", 3), ("scale", 3), ("rotation", 4), ("opacity", 1), ("color", 3))}
+        self.act = {k: torch.empty(P, n, **f32) for k, n in (("scale", 3), ("rotation", 4), ("opacity", 1))}
+        self.image = torch.empty(3, self.H, self.W, **f32)
+        self.radii = torch.empty(P, dtype=torch.int32, device=self.dev)
+        self.planes_cl = None
+        self.capacity = None
+        self.geom = self.binning = self.img = None
+        self.pinned = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self._alloc(capacity or 4 * P)
+
+    def _alloc(self, capacity):
+        g, b, i = rasterizer.workspace_sizes(self.P, self.W, self.H, int(capacity))
+        u8 = dict(dtype=torch.uint8, device=self.dev)
+        if self.geom is None:
+            self.geom, self.img = torch.empty(g, **u8), torch.empty(i, **u8)
+        self.binning = torch.empty(b, **u8)
+        self.capacity = int(capacity)
+
+    def frame(self, planes_nchw, xyz, cam, bg):
+        """Enqueue one frame on the current stream; returns the image tensor (device).  No sync.
+        Call ``check()`` afterwards (e.g. once per batch of frames) to validate the capacity."""
+        lib, p, P = self.lib, _lib.ptr, self.P
+        flat = self.dec._ensure_flat(planes_nchw)
+        cfg = self.dec._cfg_for(planes_nchw)
+        packed = flat.packed_weights()
+        if self.planes_cl is None or self.planes_cl.numel() != planes_nchw.numel():
+            self.planes_cl = torch.empty(planes_nchw.numel(), dtype=torch.float32, device=self.dev)
+        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(self.planes_cl)))
+        _lib.check(lib.ggd_decode_forward(s, C.byref(cfg), p(self.planes_cl), p(xyz), P, p(packed),
+                                          p(self.out["xyz"]), p(self.out["scale"]), p(self.out["rotation"]),
+                                          p(self.out["opacity"]), p(self.out["color"]),
+                                          p(self.act["scale"]), p(self.act["rotation"]), p(self.act["opacity"])))
+        import math
+        _lib.check(lib.ggd_raster_forward(
+            s, P, 0, 1, p(bg), self.W, self.H, p(self.out["xyz"]), p(self.out["color"]), None,
+            p(self.act["opacity"]), p(self.act["scale"]), 1.0, p(self.act["rotation"]), None,
+            p(cam.world_view_transform), p(cam.full_proj_transform), p(cam.camera_center),
+            math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), 0,
+            p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
+            C.c_void_p(self.pinned.data_ptr())))
+        return self.image
+
+    def check(self):
+        """Synchronise and verify the last frame fit the binning buffer; grows it otherwise.
+        Returns (num_rendered, overflowed)."""
+        torch.cuda.current_stream().synchronize()
+        R = int(self.pinned[0].item()) & 0xffffffff
+        over = R > self.capacity
+        if over:
+            self._alloc(int(R * 1.25) + 4096)
+        return R, over

@@ -81,3 +81,29 @@ def raster_scene(P, size=512, fov_deg=12.0, seed_offset=0, device="cpu", arch="p
     scene.update(W=size, H=size, tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5),
                  sh_degree=0, scale_modifier=1.0)
     return scene
+
+
+class _Renderer:
+    plane_axes = None      # the fused kernel hard-wires the per-arch axis permutation
+
+
+class SyntheticGenerator(torch.nn.Module):
+    """Stand-in for the upstream EG3D / PanoHead generator (out of scope):
+    ``mapping`` returns zeros, ``synthesis`` returns the given ``feature_planes``."""
+
+    def __init__(self, planes, arch="eg3d", depth=1, box_warp=1.0):
+        super().__init__()
+        self.planes = planes
+        self.rendering_kwargs = {"box_warp": box_warp}
+        if arch == "panohead":
+            self.rendering_kwargs["triplane_depth"] = depth
+        self.renderer = _Renderer()
+        self.calls = []
+
+    def mapping(self, z, c, truncation_psi=1):
+        self.calls.append(("mapping", float(c.abs().sum())))
+        return torch.zeros(1, 14, 512, device=z.device)
+
+    def synthesis(self, ws, c, noise_mode="const"):
+        self.calls.append(("synthesis", float(c.abs().sum())))
+        return {"feature_planes": self.planes}

@@ -123,6 +123,15 @@ GGD_API int ggd_mark_visible(void* stream, int P, const float* means3D, const fl
 GGD_API int ggd_raster_field(int which, const char* name, int P, int W, int H, uint64_t bin_capacity,
                      size_t* byte_offset, size_t* count);
 
+/* Per-stage device timing for benchmarks (the reference has only the debug
+ * sync-after-each-stage CHECK_CUDA, DGR/cuda_rasterizer/auxiliary.h:166-173).
+ * When enabled, every entry point records CUDA events around each stage on the
+ * caller's stream; ggd_stage_times waits for them and returns milliseconds of
+ * the LAST recorded occurrence, -1 for a stage that did not run.  Order:
+ * planes_channels_last, decode, preprocess, scan, duplicate, sort, ranges, blend. */
+GGD_API int ggd_stage_timing(int enable);
+GGD_API int ggd_stage_times(float ms_out[8]);
+
 /* ------------------------------------------------------------------------ */
 /* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs           */
 /* ------------------------------------------------------------------------ */
@@ -139,6 +148,57 @@ GGD_API int ggd_sort_pairs(void* stream, const uint64_t* keys_in, uint64_t* keys
                    const uint32_t* vals_in, uint32_t* vals_out,
                    const uint32_t* n_dev, uint64_t capacity, int begin_bit, int end_bit,
                    uint64_t* keys_tmp, uint32_t* vals_tmp, void* scratch, size_t scratch_bytes);
+
+
+/* ------------------------------------------------------------------------ */
+/* Fused tri-plane sampling + five-head decoder MLP                          */
+/* ------------------------------------------------------------------------ */
+
+/* Static description of a decoder.  Mirrors the constructor / forward
+ * arguments of the reference decoder classes
+ * (main/decoder_models/parallel_decoder.py:13-36, sequential_decoder.py:13-36,
+ * sequential_decoder_reverse.py:13-36) and the generator's rendering_kwargs
+ * (box_warp, triplane_depth). */
+typedef struct ggd_decoder_config {
+    int arch;          /* 0 = EG3D tri-planes (bilinear), 1 = PanoHead tri-grids (trilinear)  */
+    int variant;       /* 0 = parallel, 1 = sequential, 2 = sequential_reverse                */
+    int plane_depth;   /* triplane_depth D (1 for EG3D)                                       */
+    int plane_h, plane_w;
+    int pos_freqs;     /* 0 = raw xyz, 10 = Embedder(num_freqs=10) -> 63 dims                 */
+    int hidden;        /* must be 128 (the width the kernels are specialised for)             */
+    float box_warp;
+    float scale_bias;  /* activate_scale offset: -2 (parallel, sequential), -2.5 (reverse)    */
+} ggd_decoder_config;
+
+/* Number of floats of (a) the flat parameter buffer in nn.Linear layout, heads
+ * in get_params_custom() order xyz, scale, rotation, opacity, color, each
+ * W0,b0,..,W3,b3 with W[out][in] (main/decoder_models/base_decoder.py:11-19),
+ * and (b) the packed buffer ggd_decode_pack_weights produces. */
+GGD_API int ggd_decode_param_counts(const ggd_decoder_config* cfg, size_t* flat_floats, size_t* packed_floats);
+/* Offset (in floats) of one tensor inside the flat buffer: head 0..4, layer 0..3,
+ * is_bias 0/1; also returns its fan-in and fan-out. */
+GGD_API int ggd_decode_param_offset(const ggd_decoder_config* cfg, int head, int layer, int is_bias,
+                                    size_t* offset, int* fan_in, int* fan_out);
+/* Re-lays the flat parameters out for the kernels (transposed, zero padded).
+ * No counterpart call in the reference (ATen reads nn.Linear weights in place). */
+GGD_API int ggd_decode_pack_weights(void* stream, const ggd_decoder_config* cfg,
+                                    const float* flat_params, float* packed);
+/* planes: the generator's feature_planes [3][32*D][H][W] fp32 (batch 1;
+ * eg3d/training/triplane.py:93, PanoHead/training/triplane.py:224) ->
+ * channels-last [3][D][H][W][32] so one texel is one 128-byte line. */
+GGD_API int ggd_planes_channels_last(void* stream, const ggd_decoder_config* cfg,
+                                     const float* planes_nchw, float* planes_cl);
+/* sample_from_planes + (Embedder) + 5 x Decoder + scale/xyz post-math, and
+ * optionally the GaussianModel activations, for P points.  Replaces
+ * {Parallel,Sequential,SequentialReverse}Decoder.forward after G.synthesis
+ * (parallel_decoder.py:41-80) and gaussian_model.py:99-121.  Outputs are the
+ * reference's result fields: xyz[P][3] scale[P][3] rotation[P][4]
+ * opacity[P][1] color[P][3]; act_* may be NULL. */
+GGD_API int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl,
+                               const float* xyz, int P, const float* packed,
+                               float* out_xyz, float* out_scale, float* out_rotation,
+                               float* out_opacity, float* out_color,
+                               float* act_scale, float* act_rotation, float* act_opacity);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,92 @@
+"""Fused sample+decode kernel (fp32 path) through the reference-facing decoder classes,
+against golden outputs of the reference's own classes and against the CPU oracle.
+Tolerance (BASELINE north_star): decoded attributes max-abs 1e-3 in fp32."""
+import os
+import sys
+
+import pytest
+import torch
+
+from _decoder_cases import GOLDEN, HEADS, load
+from _stubs import StubG, load_flat_into
+from gaussian_gan_decoder_b200 import synthetic
+from gaussian_gan_decoder_b200.decoder_models import ParallelDecoder, SequentialDecoder, SequentialDecoderReverse
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+import decoder_oracle as do  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+CLASSES = {"parallel": ParallelDecoder, "sequential": SequentialDecoder, "sequential_reverse": SequentialDecoderReverse}
+TOL = 1e-3
+
+
+def build(case, dev):
+    G = StubG(case["planes"].to(dev), case["arch"], case["depth"])
+    dec = CLASSES[case["variant"]](G, hidden_dim=128, use_xyz_embedding=case["pos_freqs"] > 0,
+                                   use_gen_finetune=False, device=dev)
+    load_flat_into(dec, case["flat"])
+    return dec, G
+
+
+@pytest.mark.parametrize("path", GOLDEN)
+def test_matches_reference_classes(cuda, path):
+    c = load(path)
+    dec, G = build(c, cuda)
+    cam = torch.ones(1, 25, device=cuda)
+    with torch.no_grad():
+        out = dec(torch.zeros(1, 512, device=cuda), cam, c["xyz"].to(cuda), 1.0)
+    assert list(out.keys()) == list(dec.ORDER)
+    for h in HEADS:
+        err = (out[h].cpu() - c["out"][h]).abs().max().item()
+        assert err <= TOL, (h, err)
+        assert err <= 2e-5, (h, err)       # fp32 path: in practice ~1e-6
+    # camera routing quirk q2: SequentialDecoder gives the camera to mapping, the others to synthesis
+    m, s = dict(G.calls)["mapping"], dict(G.calls)["synthesis"]
+    assert (m > 0, s > 0) == ((True, False) if c["variant"] == "sequential" else (False, True))
+    act = dec.activated()
+    assert torch.allclose(act["act_scale"], torch.exp(out.scale), rtol=1e-5, atol=1e-7)
+    assert torch.allclose(act["act_rotation"], torch.nn.functional.normalize(out.rotation), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(act["act_opacity"], torch.sigmoid(out.opacity), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("arch,variant,posenc,P", [("panohead", "parallel", False, 100_000), ("eg3d", "sequential_reverse", False, 33_333),
+                                                     ("eg3d", "parallel", True, 1), ("panohead", "sequential", True, 129)])
+def test_vs_cpu_oracle_config_shapes(cuda, arch, variant, posenc, P):
+    """Full-resolution 256x256 planes (BASELINE config shapes), ragged P."""
+    g = synthetic.gen(17)
+    depth = 3 if arch == "panohead" else 1
+    planes = synthetic.planes(arch, g, res=256, depth=depth)
+    xyz = synthetic.head_shell_points(P, g)
+    torch.manual_seed(5)
+    dec = CLASSES[variant](StubG(planes.to(cuda), arch, depth), use_xyz_embedding=posenc, use_gen_finetune=False, device=cuda)
+    flat = torch.cat([p.detach().reshape(-1).cpu() for p in dec.get_params_custom()])
+    with torch.no_grad():
+        out = dec.decode(planes.to(cuda), xyz.to(cuda))
+        ref = do.decode(arch, variant, 10 if posenc else 0, flat, planes, xyz, 1.0, depth)
+    for h in HEADS:
+        err = (out[h].cpu() - ref[h]).abs().max().item()
+        assert err <= TOL and err <= 5e-5, (h, err)
+
+
+def test_state_dict_keys_match_reference_names(cuda):
+    dec = SequentialDecoderReverse(StubG(torch.zeros(1, 3, 32, 8, 8)), use_xyz_embedding=False, device=cuda)
+    keys = [k for k in dec.state_dict().keys() if not k.startswith("G.")]
+    expect = [f"{h}_decoder.backbone.{l}.{t}" for h in ("color", "opacity", "rotation", "scale", "xyz")
+              for l in (0, 2, 4, 6) for t in ("weight", "bias")]
+    assert keys == expect
+    assert dec.xyz_decoder.backbone[0].weight.shape == (128, 46) and dec.color_decoder.backbone[0].weight.shape == (128, 35)
+    assert len(dec.get_params_custom()) == 40
+    assert abs(float(dec.activate_scale(torch.zeros(1))) - (-5.0067153 - 2.5)) < 1e-4
+
+
+def test_weights_update_is_seen(cuda):
+    """The packed kernel weights follow in-place parameter updates (optimizer steps)."""
+    g = synthetic.gen(3)
+    planes = synthetic.planes("eg3d", g, res=32).to(cuda)
+    xyz = synthetic.head_shell_points(500, g).to(cuda)
+    dec = ParallelDecoder(StubG(planes), use_xyz_embedding=False, use_gen_finetune=False, device=cuda)
+    with torch.no_grad():
+        a = dec.decode(planes, xyz).color.clone()
+        dec.color_decoder.backbone[6].bias.add_(1.0)
+        b = dec.decode(planes, xyz).color
+    assert torch.allclose(b - a, torch.ones_like(a), atol=1e-5)
