@@ -79,6 +79,7 @@ class FlatParams:
                 t.data = view
                 t.grad = grad[off:off + t.numel()].view(shape)
         self.flat, self.flat_grad = flat, grad
+        self._params = [t for _, _, _, t in self._tensors(owner)]
         self._packed_version = None
 
     def in_sync(self, owner):
@@ -87,7 +88,8 @@ class FlatParams:
 
     def packed_weights(self):
         """Kernel-layout copy of the parameters, rebuilt only when the flat buffer changed."""
-        ver = self.flat._version
+        # parameters are views of the flat buffer but carry their own version counters
+        ver = sum(t._version for t in self._params)
         if self.packed is None or self.packed.device != self.flat.device or self._packed_version != ver:
             lib = _lib.load(); _bind(lib)
             if self.packed is None or self.packed.device != self.flat.device:
