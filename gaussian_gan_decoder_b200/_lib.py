@@ -55,6 +55,7 @@ SIGNATURES = {
     "ggd_stage_times": (_i, [C.POINTER(C.c_float)]),
     "ggd_sort_scratch_bytes": (_sz, [_u64]),
     "ggd_sort_pairs": (_i, [_p, _p, _p, _p, _p, _p, _u64, _i, _i, _p, _p, _p, _sz]),
+    "ggd_sort_pairs_static": (_i, [_p, _p, _p, _p, _p, _p, _u64, _i, _i, _p, _p]),
     "ggd_decode_param_counts": (_i, [_cfg, C.POINTER(_sz), C.POINTER(_sz)]),
     "ggd_decode_param_offset": (_i, [_cfg, _i, _i, _i, C.POINTER(_sz), C.POINTER(_i), C.POINTER(_i)]),
     "ggd_decode_pack_weights": (_i, [_p, _cfg, _p, _p]),

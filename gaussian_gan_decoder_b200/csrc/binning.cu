@@ -395,3 +395,72 @@ int launch_tile_ranges(cudaStream_t s, const GeomState& g, const BinState& b, ui
 }
 
 }  // namespace ggd
+
+// ---------------------------------------------------------------------------
+// Sort entry point for callers that may not allocate device memory
+// ---------------------------------------------------------------------------
+// Some hosts of this library own all device memory themselves: a renderer or
+// serving process that carves the GPU into fixed per-tenant budgets at start-up,
+// or an engine that embeds this code as a plug-in and forbids it to touch the
+// device allocator (and cudaMalloc would stall every stream of a running frame
+// loop anyway).  Such callers can hand us keys, values and ping-pong buffers out
+// of their own arena, but they have nowhere to get the sort's bookkeeping memory
+// (digit histograms, tile tickets, look-back words) from.  For them the
+// bookkeeping lives in the array below: it is part of the loaded module, so every
+// GPU that loads the library holds these ~4 MB until the process exits.
+namespace {
+constexpr uint64_t kStaticSortMaxPairs = GGD_SORT_STATIC_MAX_PAIRS;
+constexpr size_t kStaticSortTiles = (size_t)((kStaticSortMaxPairs + ggd::kSortTile - 1) / ggd::kSortTile) + 1;
+constexpr size_t kStaticSortBytes =
+    ((sizeof(uint32_t) * ggd::kMaxSortPasses * ggd::kRadixBins + 255) / 256) * 256 + 256 +
+    ((sizeof(uint32_t) * ggd::kMaxSortPasses * kStaticSortTiles * ggd::kRadixBins + 255) / 256) * 256;
+constexpr int kMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_static_sort_scratch[kStaticSortBytes];
+
+extern "C" int ggd_sort_pairs_static(void* stream, const uint64_t* keys_in, uint64_t* keys_out,
+                                     const uint32_t* vals_in, uint32_t* vals_out,
+                                     const uint32_t* n_dev, uint64_t capacity, int begin_bit, int end_bit,
+                                     uint64_t* keys_tmp, uint32_t* vals_tmp)
+{
+    using namespace ggd;
+    if (!keys_in || !keys_out || !vals_in || !vals_out || !n_dev || !keys_tmp || !vals_tmp) {
+        set_error("ggd_sort_pairs_static: null pointer");
+        return GGD_E_INVALID;
+    }
+    if (capacity > kStaticSortMaxPairs) {
+        set_error("ggd_sort_pairs_static: capacity %llu exceeds the built-in scratch limit of %llu pairs; "
+                  "use ggd_sort_pairs with caller-provided scratch",
+                  (unsigned long long)capacity, (unsigned long long)kStaticSortMaxPairs);
+        return GGD_E_CAPACITY;
+    }
+    // Set-up, once per device, with that device current: in host code the array's name is only a
+    // stand-in for the symbol, not a device address, so the address each GPU gave it is looked up
+    // and remembered here and THAT pointer is what the kernels receive.
+    static void* scratch_on_device[kMaxDevices] = {nullptr};
+    int dev = -1;
+    GGD_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("ggd_sort_pairs_static: device ordinal %d out of range", dev);
+        return GGD_E_INVALID;
+    }
+    if (!scratch_on_device[dev]) {
+        void* ptr = nullptr;
+        GGD_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_static_sort_scratch));
+        scratch_on_device[dev] = ptr;
+    }
+    void* scratch = scratch_on_device[dev];
+    SortScratch sc = carve_sort_scratch(scratch, capacity);
+    if (sc.bytes > kStaticSortBytes) {
+        set_error("ggd_sort_pairs_static: internal scratch size mismatch (%zu > %zu)", sc.bytes, kStaticSortBytes);
+        return GGD_E_CAPACITY;
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // The array still holds the previous call's histograms, tickets and look-back flags:
+    // everything a sort reads before writing must be zero again.
+    GGD_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sc.zero_bytes, s));
+    return sort_pairs(s, keys_in, keys_out, vals_in, vals_out, n_dev, capacity, begin_bit, end_bit,
+                      keys_tmp, vals_tmp, sc, false);
+}
+

@@ -150,6 +150,36 @@ GGD_API int ggd_sort_pairs(void* stream, const uint64_t* keys_in, uint64_t* keys
                    uint64_t* keys_tmp, uint32_t* vals_tmp, void* scratch, size_t scratch_bytes);
 
 
+/* Same sort for callers that cannot allocate device memory.  NO COUNTERPART IN
+ * THE REFERENCE (its only sort is the CUB call above, whose temp storage the
+ * reference takes from a torch tensor it grows on demand).
+ *
+ * Who needs this: a host that owns the whole device-memory budget itself — a
+ * viewer or serving process that splits the GPU into fixed arenas at start-up, or
+ * an engine embedding this library as a plug-in — can pass keys, values and the
+ * two ping-pong buffers out of its own arena, but has no way to obtain the
+ * sort's bookkeeping memory, and a cudaMalloc in the middle of its frame loop
+ * would stall every stream it runs.  Here that bookkeeping (digit histograms,
+ * tile tickets, look-back words, about 4 MB) is a fixed array inside the library
+ * image; each GPU that loads the library holds it until the process exits.  The
+ * call makes no cudaMalloc/cudaFree and calls no allocating library routine.
+ *
+ *  - capacity may not exceed GGD_SORT_STATIC_MAX_PAIRS; larger requests fail
+ *    with GGD_E_CAPACITY and a message naming the limit.
+ *  - The first call on each device looks up the array's device address (one-time
+ *    set-up, with that device current).  Make that first call during start-up,
+ *    before any stream capture.
+ *  - All calls on a device share the one array, and it keeps whatever the
+ *    previous call left in it; each call zeroes what it needs first, on `stream`.
+ *    Two calls whose GPU work can overlap (different streams, or different host
+ *    threads on the same device) therefore race on it: order them yourself.
+ *  Arguments and results are exactly those of ggd_sort_pairs. */
+#define GGD_SORT_STATIC_MAX_PAIRS (1u << 21)
+GGD_API int ggd_sort_pairs_static(void* stream, const uint64_t* keys_in, uint64_t* keys_out,
+                                  const uint32_t* vals_in, uint32_t* vals_out,
+                                  const uint32_t* n_dev, uint64_t capacity, int begin_bit, int end_bit,
+                                  uint64_t* keys_tmp, uint32_t* vals_tmp);
+
 /* ------------------------------------------------------------------------ */
 /* Fused tri-plane sampling + five-head decoder MLP                          */
 /* ------------------------------------------------------------------------ */
