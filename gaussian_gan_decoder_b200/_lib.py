@@ -33,7 +33,7 @@ class DecoderConfig(C.Structure):
     """ctypes mirror of ``ggd_decoder_config`` (include/ggd.h)."""
     _fields_ = [("arch", C.c_int), ("variant", C.c_int), ("plane_depth", C.c_int), ("plane_h", C.c_int),
                 ("plane_w", C.c_int), ("pos_freqs", C.c_int), ("hidden", C.c_int), ("box_warp", C.c_float),
-                ("scale_bias", C.c_float)]
+                ("scale_bias", C.c_float), ("precision", C.c_int)]
 
 
 _cfg = C.POINTER(DecoderConfig)

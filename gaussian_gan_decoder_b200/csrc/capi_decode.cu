@@ -14,6 +14,7 @@ namespace {
 int check_cfg(const ggd_decoder_config* c, DecoderLayout* L)
 {
     if (!c) { set_error("null decoder config"); return GGD_E_INVALID; }
+    if (c->precision != 0 && c->precision != 1) { set_error("precision must be 0 (fp32) or 1 (fp16 tensor core)"); return GGD_E_INVALID; }
     if (c->hidden != kHidden) { set_error("hidden_dim %d unsupported: kernels are specialised for %d", c->hidden, kHidden); return GGD_E_INVALID; }
     if (c->arch != 0 && c->arch != 1) { set_error("arch must be 0 (eg3d) or 1 (panohead)"); return GGD_E_INVALID; }
     if (c->plane_depth < 1 || (c->arch == 0 && c->plane_depth != 1)) { set_error("bad plane_depth %d for arch %d", c->plane_depth, c->arch); return GGD_E_INVALID; }
@@ -30,7 +31,7 @@ int ggd_decode_param_counts(const ggd_decoder_config* cfg, size_t* flat_floats, 
     DecoderLayout L;
     if (int e = check_cfg(cfg, &L)) return e;
     if (flat_floats) *flat_floats = L.flat_count;
-    if (packed_floats) *packed_floats = L.pk_count;
+    if (packed_floats) *packed_floats = cfg->precision == 1 ? (tc_packed_bytes(L) + 3) / 4 : L.pk_count;
     return GGD_OK;
 }
 
@@ -51,6 +52,7 @@ int ggd_decode_pack_weights(void* stream, const ggd_decoder_config* cfg, const f
     DecoderLayout L;
     if (int e = check_cfg(cfg, &L)) return e;
     if (!flat_params || !packed) { set_error("ggd_decode_pack_weights: null pointer"); return GGD_E_INVALID; }
+    if (cfg->precision == 1) return launch_pack_weights_tc(static_cast<cudaStream_t>(stream), L, flat_params, packed);
     return launch_pack_weights(static_cast<cudaStream_t>(stream), L, flat_params, packed);
 }
 
@@ -85,6 +87,7 @@ int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const float*
     GGD_CUDA_CHECK(cudaGetDevice(&dev));
     GGD_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     StageScope t(static_cast<cudaStream_t>(stream), kStDecode);
+    if (cfg->precision == 1) return launch_decode_tc(static_cast<cudaStream_t>(stream), a, sms);
     return launch_decode_fwd(static_cast<cudaStream_t>(stream), a, sms);
 }
 

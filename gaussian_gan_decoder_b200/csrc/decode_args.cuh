@@ -22,5 +22,9 @@ struct DecodeFwdArgs {
 };
 
 int launch_decode_fwd(cudaStream_t s, const DecodeFwdArgs& a, int num_sms);
+// tensor-core (fp16 tcgen05) flavour: decode_tc.cu
+int launch_decode_tc(cudaStream_t s, const DecodeFwdArgs& a, int num_sms);
+int launch_pack_weights_tc(cudaStream_t s, const DecoderLayout& L, const float* flat, void* packed);
+size_t tc_packed_bytes(const DecoderLayout& L);
 
 }  // namespace ggd

@@ -1,0 +1,103 @@
+// Kernel 1, tensor-core flavour: fused tri-plane sampling + five decoder MLPs on
+// tcgen05 (fp16 operands, fp32 accumulators in TMEM) for sm_100a.
+//
+// Replaces the same reference code as decode.cu / decode_fwd.cu (sample_from_planes,
+// Embedder, 5 x Decoder, head post-math, GaussianModel activations).
+//
+// Structure (one persistent CTA per SM, 10 warps):
+//   warps 0-3 / 4-7  two epilogue warpgroups, thread = one point (TMEM lane).  They sample
+//                    the planes into the layer-0 operand, turn accumulators into the next
+//                    layer's fp16 operand (GELU in half2 with MUFU tanh) and apply the head
+//                    post-math.  The two groups work on alternate 128-point tiles so one
+//                    group's epilogue overlaps the other group's MMAs.
+//   warp 8           one thread issues tcgen05.mma (M=128, N=128 or 16, K=16 per instruction)
+//   warp 9           one thread streams the packed fp16 weights of the current head, layer by
+//                    layer, with 1-D bulk async copies into four shared-memory slots; a slot
+//                    is refilled with the next head's layer as soon as its last MMA retired.
+// A group of T tiles (T*128 points) shares every weight load, which is what keeps the
+// L2 -> shared traffic (445 KB per head set) off the critical path.
+// Operands use the K-major, no-swizzle canonical layout (8x16-byte core matrices); biases are
+// folded into the GEMMs through a constant-one operand column.
+#include "decode_args.cuh"
+#include "sampling.cuh"
+#include "tc_ptx.cuh"
+
+namespace ggd {
+
+namespace {
+
+constexpr int kM = 128;                       // points per tile == TMEM lanes
+constexpr int kKH = kHidden + 16;             // hidden-layer K incl. the bias column block
+constexpr int kNOut = 16;                     // last layer N (>= 4 outputs, MMA minimum for M=128)
+constexpr int kAStageBytes = kM * kKH * 2;    // 36864
+constexpr int kW3Bytes = kNOut * kKH * 2;     // 4608
+constexpr int kTcThreads = 320;
+constexpr float kGeluC0 = 0.8f, kGeluC1 = 0.0348f;   // tanh-form fit to erf-GELU, max abs err 2.9e-4
+
+// byte offset of element (r, k) in a K-major no-swizzle operand with K_pad columns (fp16)
+__host__ __device__ __forceinline__ uint32_t canon(uint32_t r, uint32_t k, uint32_t K_pad)
+{
+    return (r >> 3) * (K_pad * 16) + (k >> 3) * 128 + (r & 7) * 16 + (k & 7) * 2;
+}
+
+struct TcLayout {
+    int k0;              // layer-0 K (48, or 112 with the positional embedding)
+    size_t head_bytes;   // packed bytes per head
+    size_t off[kLayers];  // byte offset of each layer inside a head block
+    size_t bytes[kLayers];
+};
+__host__ __device__ inline TcLayout tc_layout(int pos_dim)
+{
+    TcLayout t;
+    t.k0 = pos_dim == 3 ? 48 : 112;
+    t.bytes[0] = (size_t)kM * t.k0 * 2;
+    t.bytes[1] = t.bytes[2] = kAStageBytes;
+    t.bytes[3] = kW3Bytes;
+    t.off[0] = 0;
+    for (int l = 1; l < kLayers; ++l) t.off[l] = t.off[l - 1] + t.bytes[l - 1];
+    t.head_bytes = t.off[3] + t.bytes[3];
+    return t;
+}
+
+__global__ void pack_weights_tc_kernel(const DecoderLayout L, const float* __restrict__ flat, uint8_t* __restrict__ packed)
+{
+    const TcLayout t = tc_layout(L.pos_dim);
+    const int h = blockIdx.y / kLayers, l = blockIdx.y % kLayers;
+    const int in = l == 0 ? L.in_dim[h] : kHidden, out = l == kLayers - 1 ? head_out(h) : kHidden;
+    const int K = l == 0 ? t.k0 : kKH, N = l == kLayers - 1 ? kNOut : kHidden;
+    const int bias_col = l == 0 ? t.k0 - 1 : kHidden;
+    const float* W = flat + L.flat_w[h][l];
+    const float* b = flat + L.flat_b[h][l];
+    uint8_t* dst = packed + (size_t)h * t.head_bytes + t.off[l];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N * K; i += gridDim.x * blockDim.x) {
+        const int n = i / K, k = i % K;
+        float v = 0.f;
+        if (n < out) v = k < in ? W[(size_t)n * in + k] : (k == bias_col ? b[n] : 0.f);
+        *reinterpret_cast<__half*>(dst + canon(n, k, K)) = __float2half_rn(v);
+    }
+}
+
+__device__ __forceinline__ __half2 gelu_h2(__half2 x)
+{
+    const __half2 c0 = __float2half2_rn(kGeluC0), c1 = __float2half2_rn(kGeluC1), hf = __float2half2_rn(0.5f);
+    const __half2 t = __hfma2(__hmul2(x, x), c1, c0);
+    const __half2 th = ptx::tanh_h2(__hmul2(x, t));
+    const __half2 hx = __hmul2(x, hf);
+    return __hfma2(hx, th, hx);
+}
+__device__ __forceinline__ float softplus_f(float x) { return x > 20.0f ? x : log1pf(expf(x)); }
+
+}  // namespace
+
+size_t tc_packed_bytes(const DecoderLayout& L) { return tc_layout(L.pos_dim).head_bytes * kHeads; }
+
+int launch_pack_weights_tc(cudaStream_t s, const DecoderLayout& L, const float* flat, void* packed)
+{
+    pack_weights_tc_kernel<<<dim3(8, kHeads * kLayers), 256, 0, s>>>(L, flat, static_cast<uint8_t*>(packed));
+    GGD_LAUNCH_CHECK("pack_weights_tc_kernel");
+    return GGD_OK;
+}
+
+}  // namespace ggd
+
+#include "decode_tc_kernel.inl"

@@ -1,0 +1,249 @@
+// Body of the tcgen05 decode kernel (included by decode_tc.cu).
+namespace ggd {
+namespace {
+
+struct TcSmem {
+    // byte offsets into dynamic shared memory
+    uint32_t w[kLayers], a[2], base0, base_stride, total;
+};
+__host__ __device__ inline TcSmem tc_smem(const TcLayout& t, int T)
+{
+    TcSmem s;
+    uint32_t o = 256;   // barriers + tmem slot
+    for (int l = 0; l < kLayers; ++l) { s.w[l] = o; o += (uint32_t)t.bytes[l]; }
+    s.a[0] = o; o += kAStageBytes;
+    s.a[1] = o; o += kAStageBytes;
+    s.base0 = o; s.base_stride = (uint32_t)(kM * t.k0 * 2);
+    o += s.base_stride * T;
+    s.total = o;
+    return s;
+}
+
+enum { B_WFULL = 0, B_WEMPTY = 4, B_AREADY = 8, B_ACCFULL = 10, B_COUNT = 12 };
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+decode_tc_kernel(const DecodeFwdArgs a, const int T)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 128);
+    const DecoderLayout& L = a.L;
+    const TcLayout tl = tc_layout(L.pos_dim);
+    const TcSmem sm = tc_smem(tl, T);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int k0 = tl.k0;
+
+    if (tid == 0) {
+        for (int i = 0; i < 8; ++i) ptx::mbar_init(&bars[i], 1);
+        ptx::mbar_init(&bars[B_AREADY], 128); ptx::mbar_init(&bars[B_AREADY + 1], 128);
+        ptx::mbar_init(&bars[B_ACCFULL], 1); ptx::mbar_init(&bars[B_ACCFULL + 1], 1);
+        ptx::mbar_fence_init();
+    }
+    if (warp == 8) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int pts_per_group = kM * T;
+    const int groups = (a.P + pts_per_group - 1) / pts_per_group;
+
+    if (warp < 8) {
+        // =========================== epilogue / sampling warpgroups ===========================
+        const int wg = warp >> 2, r = tid & 127;
+        uint8_t* A = smem + sm.a[wg];
+        const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)wg * 256;
+        {   // constant bias-column block of the hidden operand: k = 128 is 1, k = 129..143 are 0
+            const uint4 one = make_uint4(0x00003c00u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(A + canon(r, kHidden, kKH)) = one;
+            *reinterpret_cast<uint4*>(A + canon(r, kHidden + 8, kKH)) = zero;
+        }
+        const size_t plane_stride = (size_t)a.D * a.H * a.W * kFeat;
+        uint32_t n_acc = 0;
+        const int my_tiles = (T - wg + 1) / 2;          // tiles wg, wg+2, ...
+        for (int g = blockIdx.x; g < groups; g += gridDim.x) {
+            // ---- sample my tiles into their layer-0 operands ----
+            for (int i = wg; i < T; i += 2) {
+                uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
+                const int p0 = (g * T + i) * kM;
+                const int sub = r & 7, grp = r >> 3;
+                for (int it = 0; it < kM / 16; ++it) {
+                    const int pt = it * 16 + grp, gp = p0 + pt;
+                    float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (gp < a.P) {
+                        const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp);
+                        const float y = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 1);
+                        const float z = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 2);
+                        float4 s0, s1, s2;
+                        if (a.arch == 0) {
+                            s0 = sample4(a.planes, 0, 1, a.H, a.W, x, y, 0.f, sub);
+                            s1 = sample4(a.planes + plane_stride, 0, 1, a.H, a.W, x, z, 0.f, sub);
+                            s2 = sample4(a.planes + 2 * plane_stride, 0, 1, a.H, a.W, z, x, 0.f, sub);
+                        } else {
+                            s0 = sample4(a.planes, 1, a.D, a.H, a.W, x, y, z, sub);
+                            s1 = sample4(a.planes + plane_stride, 1, a.D, a.H, a.W, x, z, y, sub);
+                            s2 = sample4(a.planes + 2 * plane_stride, 1, a.D, a.H, a.W, y, z, x, sub);
+                        }
+                        m = make_float4((s0.x + s1.x + s2.x) / 3.f, (s0.y + s1.y + s2.y) / 3.f,
+                                        (s0.z + s1.z + s2.z) / 3.f, (s0.w + s1.w + s2.w) / 3.f);
+                    }
+                    __half2 lo = __floats2half2_rn(m.x, m.y), hi = __floats2half2_rn(m.z, m.w);
+                    uint2 pk = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+                    *reinterpret_cast<uint2*>(base + canon(pt, 4 * sub, k0)) = pk;
+                }
+                // row-wise part: position (+ embedding), zeroed chain columns, constant one
+                const int gp = p0 + r;
+                float px[3] = {0.f, 0.f, 0.f};
+                if (gp < a.P) for (int j = 0; j < 3; ++j) px[j] = __ldg(a.xyz + 3 * (size_t)gp + j);
+                auto put = [&](int k, float v) { *reinterpret_cast<__half*>(base + canon(r, k, k0)) = __float2half_rn(v); };
+                for (int j = 0; j < 3; ++j) put(kFeat + j, px[j]);
+                for (int f = 0; f < a.pos_freqs; ++f) {
+                    const float freq = 1.0f + (float)f * (511.0f / 9.0f);
+                    for (int j = 0; j < 3; ++j) {
+                        put(kFeat + 3 + 6 * f + j, sinf(px[j] * freq));
+                        put(kFeat + 6 + 6 * f + j, cosf(px[j] * freq));
+                    }
+                }
+                for (int k = kFeat + L.pos_dim; k < k0 - 1; ++k) put(k, 0.f);
+                put(k0 - 1, 1.0f);
+            }
+            ptx::fence_proxy_async();
+            ptx::mbar_arrive(&bars[B_AREADY + wg]);
+
+            int chain_col = kFeat + L.pos_dim;
+            for (int hi = 0; hi < kHeads; ++hi) {
+                const int h = L.order[hi];
+                const int n_out = head_out(h);
+                for (int ti = 0; ti < my_tiles; ++ti) {
+                    const int i = wg + 2 * ti;
+                    uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
+                    const int gp = (g * T + i) * kM + r;
+                    for (int l = 0; l < kLayers; ++l) {
+                        ptx::mbar_wait(&bars[B_ACCFULL + wg], n_acc & 1);
+                        ++n_acc;
+                        ptx::tc_fence_after();
+                        if (l < kLayers - 1) {
+#pragma unroll 1
+                            for (int c = 0; c < kHidden / 32; ++c) {
+                                uint32_t v[32];
+                                ptx::tmem_ld32(trow + c * 32, v);
+                                ptx::tmem_ld_wait();
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    uint32_t o[4];
+#pragma unroll
+                                    for (int q = 0; q < 4; ++q) {
+                                        const __half2 y = gelu_h2(__floats2half2_rn(__uint_as_float(v[8 * j + 2 * q]),
+                                                                                     __uint_as_float(v[8 * j + 2 * q + 1])));
+                                        o[q] = *reinterpret_cast<const uint32_t*>(&y);
+                                    }
+                                    *reinterpret_cast<uint4*>(A + canon(r, c * 32 + 8 * j, kKH)) = make_uint4(o[0], o[1], o[2], o[3]);
+                                }
+                            }
+                        } else {
+                            uint32_t v[4];
+                            ptx::tmem_ld4(trow + kHidden, v);
+                            ptx::tmem_ld_wait();
+                            float o[4] = {__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3])};
+                            if (h == kXyz) {
+                                for (int j = 0; j < 3; ++j) o[j] = o[j] * 0.01f + (gp < a.P ? __ldg(a.xyz + 3 * (size_t)gp + j) : 0.f);
+                            }
+                            if (h == kScale) for (int j = 0; j < 3; ++j) o[j] = -softplus_f(o[j] + 5.0f) + a.scale_bias;
+                            if (gp < a.P) {
+                                for (int j = 0; j < n_out; ++j) a.out[h][(size_t)gp * n_out + j] = o[j];
+                                if (h == kScale && a.act_scale) for (int j = 0; j < 3; ++j) a.act_scale[(size_t)gp * 3 + j] = expf(o[j]);
+                                if (h == kOpacity && a.act_opacity) a.act_opacity[gp] = 1.0f / (1.0f + expf(-o[0]));
+                                if (h == kRot && a.act_rot) {
+                                    const float nrm = fmaxf(sqrtf(o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3]), 1e-12f);
+                                    for (int j = 0; j < 4; ++j) a.act_rot[(size_t)gp * 4 + j] = o[j] / nrm;
+                                }
+                            }
+                            if (L.variant != 0 && hi < kHeads - 1)
+                                for (int j = 0; j < n_out; ++j)
+                                    *reinterpret_cast<__half*>(base + canon(r, chain_col + j, k0)) = __float2half_rn(o[j]);
+                        }
+                        const bool last_of_group = (hi == kHeads - 1) && (ti == my_tiles - 1) && (l == kLayers - 1);
+                        ptx::tc_fence_before();
+                        if (!last_of_group) {
+                            ptx::fence_proxy_async();
+                            ptx::mbar_arrive(&bars[B_AREADY + wg]);
+                        }
+                    }
+                }
+                chain_col += n_out;
+            }
+        }
+    } else if (warp == 8) {
+        // ================================= MMA issuer =================================
+        if (lane == 0) {
+            uint32_t n_ready[2] = {0, 0}, n_head = 0;
+            const uint32_t id_hidden = ptx::idesc_f16(kM, kHidden), id_out = ptx::idesc_f16(kM, kNOut);
+            const uint32_t sbase = ptx::smem_u32(smem);
+            for (int g = blockIdx.x; g < groups; g += gridDim.x) {
+                for (int hi = 0; hi < kHeads; ++hi, ++n_head) {
+                    for (int p = 0; p < (T + 1) / 2; ++p) {
+                        for (int l = 0; l < kLayers; ++l) {
+                            if (p == 0) ptx::mbar_wait(&bars[B_WFULL + l], n_head & 1);
+                            for (int wg = 0; wg < 2; ++wg) {
+                                const int i = 2 * p + wg;
+                                if (i >= T) continue;
+                                ptx::mbar_wait(&bars[B_AREADY + wg], n_ready[wg] & 1);
+                                ++n_ready[wg];
+                                ptx::tc_fence_after();
+                                const int K = l == 0 ? k0 : kKH;
+                                const uint32_t a_addr = sbase + (l == 0 ? sm.base0 + (uint32_t)i * sm.base_stride : sm.a[wg]);
+                                const uint32_t b_addr = sbase + sm.w[l];
+                                const uint32_t d = tmem_base + (uint32_t)wg * 256 + (l == kLayers - 1 ? kHidden : 0);
+                                const uint32_t idesc = l == kLayers - 1 ? id_out : id_hidden;
+                                for (int s = 0; s < K / 16; ++s)
+                                    ptx::mma_f16_ss(d, ptx::smem_desc(a_addr + s * 256, 128, K * 16),
+                                                    ptx::smem_desc(b_addr + s * 256, 128, K * 16), idesc, s > 0 ? 1u : 0u);
+                                ptx::mma_commit(&bars[B_ACCFULL + wg]);
+                                if (i == T - 1) ptx::mma_commit(&bars[B_WEMPTY + l]);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    } else {
+        // ================================ weight loader ================================
+        if (lane == 0) {
+            uint32_t n_head = 0;
+            const uint8_t* packed = reinterpret_cast<const uint8_t*>(a.packed);
+            for (int g = blockIdx.x; g < groups; g += gridDim.x) {
+                for (int hi = 0; hi < kHeads; ++hi, ++n_head) {
+                    const int h = L.order[hi];
+                    for (int l = 0; l < kLayers; ++l) {
+                        if (n_head > 0) ptx::mbar_wait(&bars[B_WEMPTY + l], (n_head - 1) & 1);
+                        ptx::mbar_arrive_expect_tx(&bars[B_WFULL + l], (uint32_t)tl.bytes[l]);
+                        ptx::bulk_g2s(smem + sm.w[l], packed + (size_t)h * tl.head_bytes + tl.off[l], (uint32_t)tl.bytes[l],
+                                      &bars[B_WFULL + l]);
+                    }
+                }
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 8) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+}  // namespace
+
+int launch_decode_tc(cudaStream_t s, const DecodeFwdArgs& a, int num_sms)
+{
+    const TcLayout tl = tc_layout(a.L.pos_dim);
+    int T = 4;
+    while (T > 1 && tc_smem(tl, T).total > 227 * 1024) T >>= 1;
+    const TcSmem sm = tc_smem(tl, T);
+    if (sm.total > 227 * 1024) { set_error("decode_tc: shared memory budget exceeded (%u bytes)", sm.total); return GGD_E_INVALID; }
+    GGD_CUDA_CHECK(cudaFuncSetAttribute(decode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm.total));
+    const int groups = (a.P + kM * T - 1) / (kM * T);
+    const int grid = groups < num_sms ? groups : num_sms;
+    decode_tc_kernel<<<grid, kTcThreads, sm.total, s>>>(a, T);
+    GGD_LAUNCH_CHECK("decode_tc_kernel");
+    return GGD_OK;
+}
+
+}  // namespace ggd

@@ -43,6 +43,7 @@ class FusedDecoderBase(nn.Module):
         # reference quirk q1: SequentialDecoderReverse.forward reads self.triplane_sr, which its
         # __init__ never sets; define the only supported value for every variant.
         self.triplane_sr = "None"
+        self.precision = fused.DEFAULT_PRECISION     # "fp16" (tensor cores) or "fp32" (exact)
         self._flat = None
         self._cfg_cache = {}
         self._last_activated = None
@@ -73,17 +74,19 @@ class FusedDecoderBase(nn.Module):
         kw = self.G.rendering_kwargs
         depth = int(kw["triplane_depth"]) if "triplane_depth" in kw else 1
         arch = "panohead" if "triplane_depth" in kw else "eg3d"
-        key = (arch, depth, planes.shape[-2], planes.shape[-1], float(kw["box_warp"]))
+        key = (arch, depth, planes.shape[-2], planes.shape[-1], float(kw["box_warp"]), self.precision)
         if key not in self._cfg_cache:
             if planes.shape[2] != 32 * depth:
                 raise ValueError(f"feature_planes has {planes.shape[2]} channels, expected 32*{depth}")
             self._cfg_cache[key] = fused.make_config(arch, self.VARIANT, depth, planes.shape[-2], planes.shape[-1],
                                                      10 if self.use_xyz_embedding else 0, self.hidden_dim,
-                                                     kw["box_warp"], self.SCALE_BIAS)
+                                                     kw["box_warp"], self.SCALE_BIAS, self.precision)
         return self._cfg_cache[key]
 
     def _ensure_flat(self, planes):
         cfg = self._cfg_for(planes)
+        if self._flat is not None and self._flat.cfg.precision != cfg.precision:
+            self._flat.set_config(cfg)
         if self._flat is None:
             self._flat = fused.FlatParams(self, cfg)
         elif not self._flat.in_sync(self):

@@ -3,6 +3,7 @@ marshalling and the autograd boundary.  Everything numeric happens in
 ``libggd_b200.so`` (ggd_decode_* in include/ggd.h).
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -20,9 +21,15 @@ def _bind(lib):
     """signatures are bound by _lib.load()"""
 
 
-def make_config(arch, variant, depth, h, w, pos_freqs, hidden, box_warp, scale_bias):
+PRECISIONS = {"fp32": 0, "fp16": 1}
+# "fp16": tcgen05 tensor-core kernel (fp16 operands, fp32 accumulation) — the production path.
+# "fp32": exact CUDA-core kernel — the accuracy anchor.  Overridable per decoder (``.precision``).
+DEFAULT_PRECISION = os.environ.get("GGD_DECODE_PRECISION", "fp16")
+
+
+def make_config(arch, variant, depth, h, w, pos_freqs, hidden, box_warp, scale_bias, precision="fp32"):
     return DecoderConfig(ARCHS[arch], VARIANTS[variant], int(depth), int(h), int(w), int(pos_freqs), int(hidden),
-                         float(box_warp), float(scale_bias))
+                         float(box_warp), float(scale_bias), PRECISIONS[precision])
 
 
 def param_counts(cfg):
@@ -56,6 +63,13 @@ class FlatParams:
         self.packed = None
         self._packed_version = None
         self.adopt(owner)
+
+    def set_config(self, cfg):
+        """Switch kernel flavour (precision): same flat parameters, different packed layout."""
+        self.cfg = cfg
+        _, self.packed_count = param_counts(cfg)
+        self.packed = None
+        self._packed_version = None
 
     def _tensors(self, owner):
         for hi, h in enumerate(HEADS):

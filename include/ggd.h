@@ -198,6 +198,8 @@ typedef struct ggd_decoder_config {
     int hidden;        /* must be 128 (the width the kernels are specialised for)             */
     float box_warp;
     float scale_bias;  /* activate_scale offset: -2 (parallel, sequential), -2.5 (reverse)    */
+    int precision;     /* 0 = fp32 CUDA-core path (max-abs 1e-3 contract),
+                          1 = fp16 tcgen05 tensor-core path, fp32 accumulation (relative 1e-2 contract) */
 } ggd_decoder_config;
 
 /* Number of floats of (a) the flat parameter buffer in nn.Linear layout, heads
