@@ -4,7 +4,7 @@
 namespace ggd {
 
 int launch_pack_weights(cudaStream_t s, const DecoderLayout& L, const float* flat, float* packed);
-int launch_planes_channels_last(cudaStream_t s, const float* src, float* dst, int D, int H, int W);
+int launch_planes_channels_last(cudaStream_t s, const float* src, void* dst, int D, int H, int W, bool half_out);
 }  // namespace ggd
 #include "decode_args.cuh"
 
@@ -56,17 +56,17 @@ int ggd_decode_pack_weights(void* stream, const ggd_decoder_config* cfg, const f
     return launch_pack_weights(static_cast<cudaStream_t>(stream), L, flat_params, packed);
 }
 
-int ggd_planes_channels_last(void* stream, const ggd_decoder_config* cfg, const float* planes_nchw, float* planes_cl)
+int ggd_planes_channels_last(void* stream, const ggd_decoder_config* cfg, const float* planes_nchw, void* planes_cl)
 {
     DecoderLayout L;
     if (int e = check_cfg(cfg, &L)) return e;
     if (!planes_nchw || !planes_cl) { set_error("ggd_planes_channels_last: null pointer"); return GGD_E_INVALID; }
     StageScope t(static_cast<cudaStream_t>(stream), kStPlanes);
     return launch_planes_channels_last(static_cast<cudaStream_t>(stream), planes_nchw, planes_cl,
-                                       cfg->plane_depth, cfg->plane_h, cfg->plane_w);
+                                       cfg->plane_depth, cfg->plane_h, cfg->plane_w, cfg->precision == 1);
 }
 
-int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl,
+int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const void* planes_cl,
                        const float* xyz, int P, const float* packed,
                        float* out_xyz, float* out_scale, float* out_rotation,
                        float* out_opacity, float* out_color,
@@ -77,7 +77,7 @@ int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const float*
     if (P <= 0) { set_error("P must be positive (got %d)", P); return GGD_E_INVALID; }
     if (!planes_cl || !xyz || !packed || !out_xyz || !out_scale || !out_rotation || !out_opacity || !out_color) { set_error("ggd_decode_forward: null required pointer"); return GGD_E_INVALID; }
     if ((reinterpret_cast<uintptr_t>(planes_cl) & 15) || (reinterpret_cast<uintptr_t>(packed) & 15)) { set_error("planes_cl and packed must be 16-byte aligned"); return GGD_E_INVALID; }
-    a.planes = planes_cl; a.arch = cfg->arch; a.D = cfg->plane_depth; a.H = cfg->plane_h; a.W = cfg->plane_w;
+    a.planes = static_cast<const float*>(planes_cl); a.arch = cfg->arch; a.D = cfg->plane_depth; a.H = cfg->plane_h; a.W = cfg->plane_w;
     a.coord_scale = 2.0f / cfg->box_warp; a.pos_freqs = cfg->pos_freqs; a.scale_bias = cfg->scale_bias;
     a.xyz = xyz; a.P = P; a.packed = packed;
     a.out[kXyz] = out_xyz; a.out[kScale] = out_scale; a.out[kRot] = out_rotation;

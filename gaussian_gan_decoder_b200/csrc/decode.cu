@@ -18,6 +18,7 @@
 // k accumulation): the accuracy anchor for the tensor-core kernel and the mode
 // that meets the 1e-3 max-abs fp32 tolerance by a wide margin.
 #include "decode.cuh"
+#include <cuda_fp16.h>
 
 namespace ggd {
 
@@ -78,8 +79,9 @@ __global__ void pack_weights_kernel(const DecoderLayout L, const float* __restri
 // ---- planes: reference NCHW [3][C*D][H][W] (channel = c*D + d) -> [3][D][H][W][C] ----
 // One CTA transposes a [C=32][32 texels] slab through shared memory: reads are
 // contiguous along W, writes are contiguous 128-byte texel records.
+template <typename TOut>
 __global__ void __launch_bounds__(256)
-planes_channels_last_kernel(const float* __restrict__ src, float* __restrict__ dst, int D, int H, int W)
+planes_channels_last_kernel(const float* __restrict__ src, TOut* __restrict__ dst, int D, int H, int W)
 {
     __shared__ float tile[kFeat][33];
     const size_t HW = (size_t)H * W;
@@ -96,7 +98,7 @@ planes_channels_last_kernel(const float* __restrict__ src, float* __restrict__ d
     __syncthreads();
     for (int tt = ty; tt < 32; tt += 8) {
         const size_t t = t0 + tt;
-        if (t < HW) dst[(((size_t)plane * D + d) * HW + t) * kFeat + tx] = tile[tx][tt];
+        if (t < HW) dst[(((size_t)plane * D + d) * HW + t) * kFeat + tx] = static_cast<TOut>(tile[tx][tt]);
     }
 }
 
@@ -109,10 +111,11 @@ int launch_pack_weights(cudaStream_t s, const DecoderLayout& L, const float* fla
     return GGD_OK;
 }
 
-int launch_planes_channels_last(cudaStream_t s, const float* src, float* dst, int D, int H, int W)
+int launch_planes_channels_last(cudaStream_t s, const float* src, void* dst, int D, int H, int W, bool half_out)
 {
     const size_t slabs = (size_t)3 * D * (((size_t)H * W + 31) / 32);
-    planes_channels_last_kernel<<<(unsigned)slabs, 256, 0, s>>>(src, dst, D, H, W);
+    if (half_out) planes_channels_last_kernel<__half><<<(unsigned)slabs, 256, 0, s>>>(src, static_cast<__half*>(dst), D, H, W);
+    else planes_channels_last_kernel<float><<<(unsigned)slabs, 256, 0, s>>>(src, static_cast<float*>(dst), D, H, W);
     GGD_LAUNCH_CHECK("planes_channels_last_kernel");
     return GGD_OK;
 }

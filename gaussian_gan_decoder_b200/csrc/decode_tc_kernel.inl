@@ -66,30 +66,32 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
             for (int i = wg; i < T; i += 2) {
                 uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
                 const int p0 = (g * T + i) * kM;
-                const int sub = r & 7, grp = r >> 3;
-                for (int it = 0; it < kM / 16; ++it) {
-                    const int pt = it * 16 + grp, gp = p0 + pt;
-                    float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
+                const int sub = r & 3, grp = r >> 2;        // 4 lanes per point, 8 channels per lane
+                const __half* pl = reinterpret_cast<const __half*>(a.planes);
+                for (int it = 0; it < kM / 32; ++it) {
+                    const int pt = it * 32 + grp, gp = p0 + pt;
+                    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                     if (gp < a.P) {
                         const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp);
                         const float y = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 1);
                         const float z = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 2);
-                        float4 s0, s1, s2;
-                        if (a.arch == 0) {
-                            s0 = sample4(a.planes, 0, 1, a.H, a.W, x, y, 0.f, sub);
-                            s1 = sample4(a.planes + plane_stride, 0, 1, a.H, a.W, x, z, 0.f, sub);
-                            s2 = sample4(a.planes + 2 * plane_stride, 0, 1, a.H, a.W, z, x, 0.f, sub);
-                        } else {
-                            s0 = sample4(a.planes, 1, a.D, a.H, a.W, x, y, z, sub);
-                            s1 = sample4(a.planes + plane_stride, 1, a.D, a.H, a.W, x, z, y, sub);
-                            s2 = sample4(a.planes + 2 * plane_stride, 1, a.D, a.H, a.W, y, z, x, sub);
+                        if (a.arch == 0) {   // (x,y) (x,z) (z,x)
+                            sample8h<1>(pl, 1, a.H, a.W, x, y, 0.f, sub, acc);
+                            sample8h<1>(pl + plane_stride, 1, a.H, a.W, x, z, 0.f, sub, acc);
+                            sample8h<1>(pl + 2 * plane_stride, 1, a.H, a.W, z, x, 0.f, sub, acc);
+                        } else {             // (x,y,z) (x,z,y) (y,z,x) -> (W,H,D)
+                            sample8h<2>(pl, a.D, a.H, a.W, x, y, z, sub, acc);
+                            sample8h<2>(pl + plane_stride, a.D, a.H, a.W, x, z, y, sub, acc);
+                            sample8h<2>(pl + 2 * plane_stride, a.D, a.H, a.W, y, z, x, sub, acc);
                         }
-                        m = make_float4((s0.x + s1.x + s2.x) / 3.f, (s0.y + s1.y + s2.y) / 3.f,
-                                        (s0.z + s1.z + s2.z) / 3.f, (s0.w + s1.w + s2.w) / 3.f);
                     }
-                    __half2 lo = __floats2half2_rn(m.x, m.y), hi = __floats2half2_rn(m.z, m.w);
-                    uint2 pk = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
-                    *reinterpret_cast<uint2*>(base + canon(pt, 4 * sub, k0)) = pk;
+                    uint32_t pk[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const __half2 hv = __floats2half2_rn(acc[2 * q] / 3.f, acc[2 * q + 1] / 3.f);
+                        pk[q] = *reinterpret_cast<const uint32_t*>(&hv);
+                    }
+                    *reinterpret_cast<uint4*>(base + canon(pt, 8 * sub, k0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 }
                 // row-wise part: position (+ embedding), zeroed chain columns, constant one
                 const int gp = p0 + r;

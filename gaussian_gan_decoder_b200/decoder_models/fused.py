@@ -134,7 +134,7 @@ def decode_forward(cfg, planes_nchw, xyz, packed, with_activations=True):
     p = _lib.ptr
     with torch.cuda.device(dev):
         s = _stream()
-        planes_cl = torch.empty(planes_nchw.numel(), dtype=torch.float32, device=dev)
+        planes_cl = torch.empty(planes_nchw.numel() * (2 if cfg.precision == 1 else 4), dtype=torch.uint8, device=dev)
         _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(planes_cl)))
         _lib.check(lib.ggd_decode_forward(s, C.byref(cfg), p(planes_cl), p(xyz), P, p(packed),
                                           p(out["xyz"]), p(out["scale"]), p(out["rotation"]), p(out["opacity"]),

@@ -47,8 +47,9 @@ class FramePipeline:
         flat = self.dec._ensure_flat(planes_nchw)
         cfg = self.dec._cfg_for(planes_nchw)
         packed = flat.packed_weights()
-        if self.planes_cl is None or self.planes_cl.numel() != planes_nchw.numel():
-            self.planes_cl = torch.empty(planes_nchw.numel(), dtype=torch.float32, device=self.dev)
+        nbytes = planes_nchw.numel() * (2 if cfg.precision == 1 else 4)
+        if self.planes_cl is None or self.planes_cl.numel() != nbytes:
+            self.planes_cl = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
         s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(self.planes_cl)))
         _lib.check(lib.ggd_decode_forward(s, C.byref(cfg), p(self.planes_cl), p(xyz), P, p(packed),

@@ -217,16 +217,17 @@ GGD_API int ggd_decode_pack_weights(void* stream, const ggd_decoder_config* cfg,
                                     const float* flat_params, float* packed);
 /* planes: the generator's feature_planes [3][32*D][H][W] fp32 (batch 1;
  * eg3d/training/triplane.py:93, PanoHead/training/triplane.py:224) ->
- * channels-last [3][D][H][W][32] so one texel is one 128-byte line. */
+ * channels-last [3][D][H][W][32], fp32 (precision 0: one texel = one 128-byte
+ * line) or fp16 (precision 1: 64 bytes per texel). */
 GGD_API int ggd_planes_channels_last(void* stream, const ggd_decoder_config* cfg,
-                                     const float* planes_nchw, float* planes_cl);
+                                     const float* planes_nchw, void* planes_cl);
 /* sample_from_planes + (Embedder) + 5 x Decoder + scale/xyz post-math, and
  * optionally the GaussianModel activations, for P points.  Replaces
  * {Parallel,Sequential,SequentialReverse}Decoder.forward after G.synthesis
  * (parallel_decoder.py:41-80) and gaussian_model.py:99-121.  Outputs are the
  * reference's result fields: xyz[P][3] scale[P][3] rotation[P][4]
  * opacity[P][1] color[P][3]; act_* may be NULL. */
-GGD_API int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl,
+GGD_API int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const void* planes_cl,
                                const float* xyz, int P, const float* packed,
                                float* out_xyz, float* out_scale, float* out_rotation,
                                float* out_opacity, float* out_color,
