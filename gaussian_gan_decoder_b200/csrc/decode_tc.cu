@@ -4,14 +4,15 @@
 // Replaces the same reference code as decode.cu / decode_fwd.cu (sample_from_planes,
 // Embedder, 5 x Decoder, head post-math, GaussianModel activations).
 //
-// Structure (one persistent CTA per SM, 10 warps):
-//   warps 0-3 / 4-7  two epilogue warpgroups, thread = one point (TMEM lane).  They sample
-//                    the planes into the layer-0 operand, turn accumulators into the next
-//                    layer's fp16 operand (GELU in half2 with MUFU tanh) and apply the head
-//                    post-math.  The two groups work on alternate 128-point tiles so one
-//                    group's epilogue overlaps the other group's MMAs.
-//   warp 8           one thread issues tcgen05.mma (M=128, N=128 or 16, K=16 per instruction)
-//   warp 9           one thread streams the packed fp16 weights of the current head, layer by
+// Structure (one persistent CTA per SM, 18 warps):
+//   warps 0-7 / 8-15 two epilogue groups of 8 warps; thread = one point (TMEM lane) x one half
+//                    of the 128 accumulator columns.  They sample the planes into the layer-0
+//                    operand, turn accumulators into the next layer's fp16 operand (GELU in
+//                    half2 with MUFU tanh) and apply the head post-math.  The two groups work
+//                    on alternate 128-point tiles so one group's epilogue overlaps the other
+//                    group's MMAs.
+//   warp 16          one thread issues tcgen05.mma (M=128, N=128 or 16, K=16 per instruction)
+//   warp 17          one thread streams the packed fp16 weights of the current head, layer by
 //                    layer, with 1-D bulk async copies into four shared-memory slots; a slot
 //                    is refilled with the next head's layer as soon as its last MMA retired.
 // A group of T tiles (T*128 points) shares every weight load, which is what keeps the
@@ -31,7 +32,7 @@ constexpr int kKH = kHidden + 16;             // hidden-layer K incl. the bias c
 constexpr int kNOut = 16;                     // last layer N (>= 4 outputs, MMA minimum for M=128)
 constexpr int kAStageBytes = kM * kKH * 2;    // 36864
 constexpr int kW3Bytes = kNOut * kKH * 2;     // 4608
-constexpr int kTcThreads = 320;
+constexpr int kTcThreads = 576;             // 16 epilogue warps + MMA warp + loader warp
 constexpr float kGeluC0 = 0.8f, kGeluC1 = 0.0348f;   // tanh-form fit to erf-GELU, max abs err 2.9e-4
 
 // byte offset of element (r, k) in a K-major no-swizzle operand with K_pad columns (fp16)

@@ -35,11 +35,11 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
 
     if (tid == 0) {
         for (int i = 0; i < 8; ++i) ptx::mbar_init(&bars[i], 1);
-        ptx::mbar_init(&bars[B_AREADY], 128); ptx::mbar_init(&bars[B_AREADY + 1], 128);
+        ptx::mbar_init(&bars[B_AREADY], 256); ptx::mbar_init(&bars[B_AREADY + 1], 256);
         ptx::mbar_init(&bars[B_ACCFULL], 1); ptx::mbar_init(&bars[B_ACCFULL + 1], 1);
         ptx::mbar_fence_init();
     }
-    if (warp == 8) ptx::tmem_alloc<512>(tmem_slot);
+    if (warp == 16) ptx::tmem_alloc<512>(tmem_slot);
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -48,12 +48,13 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
     const int pts_per_group = kM * T;
     const int groups = (a.P + pts_per_group - 1) / pts_per_group;
 
-    if (warp < 8) {
-        // =========================== epilogue / sampling warpgroups ===========================
-        const int wg = warp >> 2, r = tid & 127;
+    if (warp < 16) {
+        // ====================== epilogue / sampling: 8 warps per ping-pong slot ======================
+        // Two warps share every TMEM lane quarter and split the 128 accumulator columns in halves.
+        const int wg = warp >> 3, e = tid & 255, r = e & 127, colhalf = e >> 7;
         uint8_t* A = smem + sm.a[wg];
         const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)wg * 256;
-        {   // constant bias-column block of the hidden operand: k = 128 is 1, k = 129..143 are 0
+        if (colhalf == 0) {   // constant bias-column block of the hidden operand: k = 128 is 1, k = 129..143 are 0
             const uint4 one = make_uint4(0x00003c00u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);
             *reinterpret_cast<uint4*>(A + canon(r, kHidden, kKH)) = one;
             *reinterpret_cast<uint4*>(A + canon(r, kHidden + 8, kKH)) = zero;
@@ -66,10 +67,10 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
             for (int i = wg; i < T; i += 2) {
                 uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
                 const int p0 = (g * T + i) * kM;
-                const int sub = r & 3, grp = r >> 2;        // 4 lanes per point, 8 channels per lane
+                const int sub = e & 3, grp = e >> 2;        // 4 lanes per point, 8 channels per lane
                 const __half* pl = reinterpret_cast<const __half*>(a.planes);
-                for (int it = 0; it < kM / 32; ++it) {
-                    const int pt = it * 32 + grp, gp = p0 + pt;
+                for (int it = 0; it < kM / 64; ++it) {
+                    const int pt = it * 64 + grp, gp = p0 + pt;
                     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                     if (gp < a.P) {
                         const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp);
@@ -94,6 +95,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                     *reinterpret_cast<uint4*>(base + canon(pt, 8 * sub, k0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 }
                 // row-wise part: position (+ embedding), zeroed chain columns, constant one
+                if (colhalf != 0) continue;
                 const int gp = p0 + r;
                 float px[3] = {0.f, 0.f, 0.f};
                 if (gp < a.P) for (int j = 0; j < 3; ++j) px[j] = __ldg(a.xyz + 3 * (size_t)gp + j);
@@ -126,7 +128,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                         ptx::tc_fence_after();
                         if (l < kLayers - 1) {
 #pragma unroll 1
-                            for (int c = 0; c < kHidden / 32; ++c) {
+                            for (int c = colhalf * 2; c < colhalf * 2 + 2; ++c) {
                                 uint32_t v[32];
                                 ptx::tmem_ld32(trow + c * 32, v);
                                 ptx::tmem_ld_wait();
@@ -142,7 +144,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                                     *reinterpret_cast<uint4*>(A + canon(r, c * 32 + 8 * j, kKH)) = make_uint4(o[0], o[1], o[2], o[3]);
                                 }
                             }
-                        } else {
+                        } else if (colhalf == 0) {
                             uint32_t v[4];
                             ptx::tmem_ld4(trow + kHidden, v);
                             ptx::tmem_ld_wait();
@@ -175,7 +177,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                 chain_col += n_out;
             }
         }
-    } else if (warp == 8) {
+    } else if (warp == 16) {
         // ================================= MMA issuer =================================
         if (lane == 0) {
             uint32_t n_ready[2] = {0, 0}, n_head = 0;
@@ -228,7 +230,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
     }
     ptx::tc_fence_before();
     __syncthreads();
-    if (warp == 8) ptx::tmem_dealloc<512>(tmem_base);
+    if (warp == 16) ptx::tmem_dealloc<512>(tmem_base);
 }
 
 }  // namespace
