@@ -188,6 +188,21 @@ onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ key
     if (tile_base >= n) return;
     const uint32_t n_valid = (uint32_t)min((uint64_t)kSortTile, (uint64_t)n - tile_base);
 
+    // ---- trivial digit: if one bin holds every key (e.g. the exponent byte of depths that all lie
+    // in [2,4), or tile-id bits above the tile count) the pass is the identity permutation: copy
+    // the tile to the other buffer and skip ranking, look-back and scatter.
+    if (__syncthreads_or(__ldg(hist + t) == n)) {
+#pragma unroll
+        for (int k = 0; k < kSortItems; ++k) {
+            const uint32_t li = t + k * kSortThreads;
+            if (li < n_valid) {
+                keys_out[tile_base + li] = __ldg(keys_in + tile_base + li);
+                vals_out[tile_base + li] = __ldg(vals_in + tile_base + li);
+            }
+        }
+        return;
+    }
+
     // ---- load (warp-striped: item k of lane l sits at warp_base + k*32 + l)
     uint64_t key[kSortItems];
     const uint32_t warp_base = warp * (32 * kSortItems);

@@ -11,13 +11,44 @@
 // {xy, conic, opacity, rgb} in shared memory as two float4 + one float, so the
 // inner loop has no global loads at all (the reference gathers the colour from
 // global memory for every contributing (pixel, Gaussian) pair, forward.cu:355)
-// and every shared-memory read is a 16-byte broadcast.
+// and every shared-memory read is a 16-byte broadcast; and each warp owns an
+// 8x4 pixel block and only walks the instances whose conservative footprint
+// touches that block (see warp_block_mask).
 #include "common.cuh"
 
 namespace ggd {
 namespace {
 
 constexpr int kBatch = kTilePixels;  // 256 instances staged per round
+
+// Conservative footprint test.  An instance can only change a pixel if
+// alpha = min(0.99, o * exp(power)) >= 1/255, i.e. d^T Q d <= 2 ln(255 o) with Q the conic.
+// The staging thread turns that ellipse into a pixel-space box, inflated by 1 % (the fp32
+// evaluation of `power` in the blend loop is accurate to ~4e-4 relative once the conic's
+// condition number is bounded, which is checked: ill-conditioned conics are never culled),
+// and records which of the eight 8x4-pixel warp blocks the box touches.  A warp then walks
+// only the instances whose bit is set.  Skipped (pixel, instance) pairs are exactly pairs the
+// reference rejects with `alpha < 1/255`, so T, C, n_contrib keep their reference bits; the
+// contributor index is recovered from the instance's position in the tile list.
+__device__ __forceinline__ uint32_t warp_block_mask(float x, float y, float a, float b, float c, float o,
+                                                    float tile_x0, float tile_y0)
+{
+    if (!(o >= 1.0f / 255.0f)) return (o == o) ? 0u : 0xffu;   // alpha <= o < 1/255: never accepted (NaN: keep)
+    const float det = a * c - b * b, tr = a + c;
+    if (!(det > 0.f) || !(tr * tr <= 1000.f * det) || !(o <= 1e30f)) return 0xffu;
+    const float s = 2.02f * logf(255.0f * o) + 1e-4f;
+    const float inv = 1.0f / det;
+    const float rx = sqrtf(s * c * inv) * 1.005f + 1e-3f, ry = sqrtf(s * a * inv) * 1.005f + 1e-3f;
+    const float lx0 = x - rx - tile_x0, lx1 = x + rx - tile_x0, ly0 = y - ry - tile_y0, ly1 = y + ry - tile_y0;
+    if (!(lx0 == lx0) || !(lx1 == lx1) || !(ly0 == ly0) || !(ly1 == ly1)) return 0xffu;
+    uint32_t m = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        const float bx0 = (float)((w & 1) * 8), by0 = (float)((w >> 1) * 4);
+        if (lx1 >= bx0 && lx0 <= bx0 + 7.f && ly1 >= by0 && ly0 <= by0 + 3.f) m |= 1u << w;
+    }
+    return m;
+}
 
 __global__ void __launch_bounds__(kTilePixels)
 blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
@@ -29,22 +60,25 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
     __shared__ float4 s_a[kBatch];  // x, y, conic.x, conic.y
     __shared__ float4 s_b[kBatch];  // conic.z, opacity, r, g
     __shared__ float s_c[kBatch];   // b
+    __shared__ uint32_t s_mask[kBatch];
 
     const uint32_t tiles_x = (W + kTileX - 1) / kTileX;
-    const uint32_t px = blockIdx.x * kTileX + threadIdx.x;
-    const uint32_t py = blockIdx.y * kTileY + threadIdx.y;
+    const int tr = threadIdx.x, warp = tr >> 5, lane = tr & 31;
+    // warp w owns the 8x4 pixel block at (8*(w&1), 4*(w>>1)) of the tile
+    const uint32_t px = blockIdx.x * kTileX + (warp & 1) * 8 + (lane & 7);
+    const uint32_t py = blockIdx.y * kTileY + (warp >> 1) * 4 + (lane >> 3);
     const uint32_t pix_id = W * py + px;
     const float fx = (float)px, fy = (float)py;
+    const float tile_x0 = (float)(blockIdx.x * kTileX), tile_y0 = (float)(blockIdx.y * kTileY);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     bool done = !inside;
-    const int tr = threadIdx.y * kTileX + threadIdx.x;
 
     const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
     const int rounds = (int)((range.y - range.x + kBatch - 1) / kBatch);
     int to_do = (int)(range.y - range.x);
 
     float T = 1.0f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
     float C0 = 0.f, C1 = 0.f, C2 = 0.f;
 
     for (int i = 0; i < rounds; ++i, to_do -= kBatch) {
@@ -60,33 +94,41 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
             s_a[tr] = make_float4(xy.x, xy.y, co.x, co.y);
             s_b[tr] = make_float4(co.z, co.w, r, g);
             s_c[tr] = b;
+            s_mask[tr] = warp_block_mask(xy.x, xy.y, co.x, co.y, co.z, co.w, tile_x0, tile_y0);
         }
         __syncthreads();
 
         const int lim = min(kBatch, to_do);
-        for (int j = 0; !done && j < lim; ++j) {
-            contributor++;
-            const float4 A = s_a[j];
-            const float4 B = s_b[j];
-            // Every product/sum below is pinned (_rn intrinsics are never re-fused by ptxas) to
-            // the FMA placement of the reference build: q = fma(dx, cx*dx, cz*dy*dy),
-            // power = fma(q, -0.5, -(cy*dx*dy)), C = fma(T, alpha*c, C).
-            const float dx = __fsub_rn(A.x, fx), dy = __fsub_rn(A.y, fy);
-            const float q = __fmaf_rn(dx, __fmul_rn(dx, A.z), __fmul_rn(dy, __fmul_rn(dy, B.x)));
-            const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, A.w)));
-            if (power > 0.0f) continue;
-            const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-            if (test_T < 0.0001f) {
-                done = true;
-                continue;
+        for (int j0 = 0; j0 < lim; j0 += 32) {
+            if (__all_sync(0xffffffffu, done)) break;
+            const bool hit = (j0 + lane < lim) && ((s_mask[j0 + lane] >> warp) & 1u);
+            uint32_t bits = __ballot_sync(0xffffffffu, hit);
+            while (bits) {
+                const int j = j0 + __ffs(bits) - 1;
+                bits &= bits - 1;
+                if (done) continue;
+                const float4 A = s_a[j];
+                const float4 B = s_b[j];
+                // Every product/sum below is pinned (_rn intrinsics are never re-fused by ptxas) to
+                // the FMA placement of the reference build: q = fma(dx, cx*dx, cz*dy*dy),
+                // power = fma(q, -0.5, -(cy*dx*dy)), C = fma(T, alpha*c, C).
+                const float dx = __fsub_rn(A.x, fx), dy = __fsub_rn(A.y, fy);
+                const float q = __fmaf_rn(dx, __fmul_rn(dx, A.z), __fmul_rn(dy, __fmul_rn(dy, B.x)));
+                const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, A.w)));
+                if (power > 0.0f) continue;
+                const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+                if (test_T < 0.0001f) {
+                    done = true;
+                    continue;
+                }
+                C0 = __fmaf_rn(T, __fmul_rn(alpha, B.z), C0);
+                C1 = __fmaf_rn(T, __fmul_rn(alpha, B.w), C1);
+                C2 = __fmaf_rn(T, __fmul_rn(alpha, s_c[j]), C2);
+                T = test_T;
+                last_contributor = (uint32_t)(i * kBatch + j + 1);
             }
-            C0 = __fmaf_rn(T, __fmul_rn(alpha, B.z), C0);
-            C1 = __fmaf_rn(T, __fmul_rn(alpha, B.w), C1);
-            C2 = __fmaf_rn(T, __fmul_rn(alpha, s_c[j]), C2);
-            T = test_T;
-            last_contributor = contributor;
         }
     }
 
@@ -106,7 +148,7 @@ int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const Geo
                  const BinState& b, const ImgState& im, const float* features,
                  const float* background, float* out_color)
 {
-    dim3 grid(grid_x, grid_y, 1), block(kTileX, kTileY, 1);
+    dim3 grid(grid_x, grid_y, 1), block(kTilePixels, 1, 1);
     blend_kernel<<<grid, block, 0, s>>>(im.ranges, b.vals, W, H, g.means2D, features,
                                         g.conic_opacity, im.accum_alpha, im.n_contrib, background,
                                         out_color);
