@@ -100,6 +100,27 @@ GGD_API int ggd_raster_forward(void* stream, int P, int D, int M, const float* b
                        void* geom_ws, void* bin_ws, uint64_t bin_capacity, void* img_ws,
                        float* out_color, int* radii, uint32_t* num_rendered_host);
 
+/* Backward of ggd_raster_forward.  Replaces CudaRasterizer::Rasterizer::backward
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:340-435): BACKWARD::render -> renderCUDA
+ * (backward.cu:399-557), computeCov2DCUDA (:144-274), preprocessCUDA (:346-396).
+ * Inputs are the forward's inputs plus its three state buffers (same bin_capacity)
+ * and dL/dpixel [3][H][W].  Every output must be ZERO-FILLED by the caller, as the
+ * reference's binding does (DGR/rasterize_points.cu:151-159); shapes follow it:
+ * dL_dmean2D [P][3] (only .xy written), dL_dconic [P][2][2] (slots 0,1,3),
+ * dL_dopacity [P], dL_dcolor [P][3], dL_dmean3D [P][3], dL_dcov3D [P][6],
+ * dL_dsh [P][M][3], dL_dscale [P][3], dL_drot [P][4] (no quaternion-norm
+ * Jacobian, like backward.cu:340).  Sums are floating point: results agree with
+ * the reference to rounding (its own atomics are order-nondeterministic). */
+GGD_API int ggd_raster_backward(void* stream, int P, int D, int M, const float* background, int W, int H,
+                                const float* means3D, const float* shs, const float* colors_precomp,
+                                const float* scales, float scale_modifier, const float* rotations,
+                                const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                                const void* geom_ws, const void* bin_ws, uint64_t bin_capacity, const void* img_ws,
+                                const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                                float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                                float* dL_dscale, float* dL_drot);
+
 /* Blocking read-back of { num_rendered, overflow_flag } from geom_ws
  * (synchronises `stream`).  The reference returns num_rendered from forward
  * (rasterizer_impl.cu:336); here it is a separate, optional query. */

@@ -1,0 +1,107 @@
+"""Rasteriser backward (blend replay + per-Gaussian chain) against the reference CUDA backward
+and against golden gradients captured from it.  Gradients are float sums (the reference uses
+order-nondeterministic atomics), so the comparison is tolerance based: per tensor, every element
+within 2e-3 of the tensor's max magnitude, and 99.9 % within 1e-4 of it."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from _harness import RefCuda, ref_cuda_available, run_ours
+from gaussian_gan_decoder_b200 import synthetic
+from gaussian_gan_decoder_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer, _C
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+NAMES = ["dL_dmean2D", "dL_dcolor", "dL_dopacity", "dL_dmean3D", "dL_dcov3D", "dL_dsh", "dL_dscale", "dL_drot"]
+
+
+def to_dev(scene, dev):
+    return {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in scene.items()}
+
+
+def ours_backward(scene, dL, dev):
+    o = run_ours(scene, dev)
+    geom, binning, img = o["_buffers"]
+    e = torch.empty(0, device=dev)
+    g = lambda k: scene[k] if scene.get(k) is not None else e
+    grads = _C.rasterize_gaussians_backward(
+        g("bg"), g("means3D"), o["radii"], g("colors_precomp"), g("scales"), g("rotations"),
+        scene.get("scale_modifier", 1.0), g("cov3D_precomp"), g("viewmatrix"), g("projmatrix"), scene["tanfovx"],
+        scene["tanfovy"], dL, g("shs"), scene.get("sh_degree", 0), g("campos"), geom, o["R"], binning, img, False)
+    torch.cuda.synchronize()
+    return dict(zip(NAMES, grads))
+
+
+def close(a, b, name):
+    a, b = a.reshape(-1).double().cpu(), b.reshape(-1).double().cpu()
+    assert a.shape == b.shape, name
+    scale = b.abs().max().item() + 1e-30
+    err = (a - b).abs() / scale
+    assert err.max().item() <= 2e-3, (name, err.max().item())
+    assert torch.quantile(err[:2_000_000], 0.999).item() <= 1e-4, (name, torch.quantile(err[:2_000_000], 0.999).item())
+
+
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("P,size,fov,trained", [(257, 100, 12.0, True), (5000, 256, 12.0, True), (100_000, 512, 12.0, True),
+                                                 (100_000, 512, 12.0, False)])
+def test_vs_reference_cuda_backward(cuda, P, size, fov, trained):
+    s = synthetic.raster_scene(P, size=size, fov_deg=fov, seed_offset=P % 89)
+    if not trained:
+        g = synthetic.gen(P)
+        s["scales"] = torch.exp(-7.0 + 0.1 * torch.randn(P, 3, generator=g))
+        s["opacities"] = torch.sigmoid(0.2 * torch.randn(P, 1, generator=g))
+    s = to_dev(s, cuda)
+    gen = torch.Generator(device="cpu"); gen.manual_seed(P)
+    dL = torch.randn(3, size, size, generator=gen).to(cuda)
+    ref = RefCuda()
+    ref.forward(s, cuda)
+    gr = ref.backward(dL, cuda)
+    go = ours_backward(s, dL, cuda)
+    for n in NAMES:
+        close(go[n], gr[n], n)
+
+
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+def test_sh_degree3_and_precomputed_inputs(cuda):
+    P = 4000
+    base = to_dev(synthetic.raster_scene(P, size=160, seed_offset=5), cuda)
+    g = synthetic.gen(9)
+    dL = torch.randn(3, 160, 160, generator=g).to(cuda)
+    s = dict(base); s["shs"] = (0.3 * torch.randn(P, 16, 3, generator=g)).to(cuda); s["sh_degree"] = 3
+    ref = RefCuda(); ref.forward(s, cuda); gr = ref.backward(dL, cuda); go = ours_backward(s, dL, cuda)
+    for n in NAMES:
+        close(go[n], gr[n], n)
+    s = dict(base); s["colors_precomp"] = torch.rand(P, 3, generator=g).to(cuda); s["shs"] = None
+    ref.forward(s, cuda); gr = ref.backward(dL, cuda); go = ours_backward(s, dL, cuda)
+    for n in ("dL_dmean2D", "dL_dcolor", "dL_dopacity", "dL_dmean3D", "dL_dscale", "dL_drot"):
+        close(go[n], gr[n], n)
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(HERE, "golden", "raster_*.npz"))))
+def test_autograd_path_matches_golden_reference_gradients(cuda, path):
+    """GaussianRasterizer(...)(...) -> loss.backward(): the route render_simple takes."""
+    z = np.load(path)
+    t = lambda k: torch.from_numpy(z["in_" + k]).to(cuda)
+    means3D, opac, scales, rots, shs = (t(k).requires_grad_(True) for k in ("means3D", "opacities", "scales", "rotations", "shs"))
+    means2D = torch.zeros_like(means3D, requires_grad=True)
+    rs = GaussianRasterizationSettings(int(z["H"]), int(z["W"]), float(z["tanfovx"]), float(z["tanfovy"]), t("bg"), 1.0,
+                                       t("viewmatrix"), t("projmatrix"), 0, t("campos"), False, False)
+    color, radii = GaussianRasterizer(rs)(means3D=means3D, means2D=means2D, shs=shs, opacities=opac, scales=scales,
+                                          rotations=rots)
+    assert np.array_equal(radii.cpu().numpy(), z["radii"])
+    assert np.array_equal(color.detach().cpu().numpy().view(np.int32), z["out_color"].view(np.int32))   # bit-exact forward
+    (color * t("dL_dpix")).sum().backward()
+    for ours, name in ((means3D.grad, "dL_dmean3D"), (opac.grad, "dL_dopacity"), (scales.grad, "dL_dscale"),
+                       (rots.grad, "dL_drot"), (shs.grad, "dL_dsh"), (means2D.grad, "dL_dmean2D")):
+        close(ours, torch.from_numpy(z[name]), name)
+
+
+def test_all_culled_gives_zero_gradients(cuda):
+    s = to_dev(synthetic.raster_scene(64, size=64), cuda)
+    s["means3D"] = s["means3D"] + 100.0
+    go = ours_backward(s, torch.ones(3, 64, 64, device=cuda), cuda)
+    for n in NAMES:
+        assert float(go[n].abs().sum()) == 0.0, n
