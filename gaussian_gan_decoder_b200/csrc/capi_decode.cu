@@ -7,6 +7,7 @@ int launch_pack_weights(cudaStream_t s, const DecoderLayout& L, const float* fla
 int launch_planes_channels_last(cudaStream_t s, const float* src, void* dst, int D, int H, int W, bool half_out);
 }  // namespace ggd
 #include "decode_args.cuh"
+#include "decode_bwd.cuh"
 
 using namespace ggd;
 
@@ -89,6 +90,45 @@ int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, const void* 
     StageScope t(static_cast<cudaStream_t>(stream), kStDecode);
     if (cfg->precision == 1) return launch_decode_tc(static_cast<cudaStream_t>(stream), a, sms);
     return launch_decode_fwd(static_cast<cudaStream_t>(stream), a, sms);
+}
+
+size_t ggd_decode_backward_scratch_bytes(const ggd_decoder_config* cfg, int P)
+{
+    DecoderLayout L;
+    if (check_cfg(cfg, &L) || P <= 0) return 0;
+    return bwd_stage(L.pos_dim, (size_t)P).bytes;
+}
+
+int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl_f32,
+                        const float* xyz, int P, const float* flat_params, const float* packed_f32,
+                        const float* out_xyz, const float* out_scale, const float* out_rotation,
+                        const float* out_opacity, const float* out_color,
+                        const float* dL_dxyz, const float* dL_dscale, const float* dL_drotation,
+                        const float* dL_dopacity, const float* dL_dcolor,
+                        void* scratch, size_t scratch_bytes, float* dflat, float* dplanes)
+{
+    DecodeBwdArgs a;
+    if (int e = check_cfg(cfg, &a.L)) return e;
+    if (P <= 0) { set_error("P must be positive (got %d)", P); return GGD_E_INVALID; }
+    if (!planes_cl_f32 || !xyz || !flat_params || !packed_f32 || !scratch || !dflat) { set_error("ggd_decode_backward: null required pointer"); return GGD_E_INVALID; }
+    if (a.L.variant != 0 && (!out_xyz || !out_scale || !out_rotation || !out_opacity || !out_color)) { set_error("ggd_decode_backward: chained variants need the forward results"); return GGD_E_INVALID; }
+    const BwdStage st = bwd_stage(a.L.pos_dim, (size_t)P);
+    if (scratch_bytes < st.bytes) { set_error("ggd_decode_backward: scratch too small (%zu < %zu)", scratch_bytes, st.bytes); return GGD_E_CAPACITY; }
+    if (reinterpret_cast<uintptr_t>(scratch) & 127) { set_error("scratch must be 128-byte aligned"); return GGD_E_INVALID; }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    a.planes = planes_cl_f32; a.arch = cfg->arch; a.D = cfg->plane_depth; a.H = cfg->plane_h; a.W = cfg->plane_w;
+    a.coord_scale = 2.0f / cfg->box_warp; a.pos_freqs = cfg->pos_freqs; a.xyz = xyz; a.P = P;
+    a.packed = packed_f32; a.flat = flat_params;
+    a.out[kXyz] = out_xyz; a.out[kScale] = out_scale; a.out[kRot] = out_rotation; a.out[kOpacity] = out_opacity; a.out[kColor] = out_color;
+    a.dout[kXyz] = dL_dxyz; a.dout[kScale] = dL_dscale; a.dout[kRot] = dL_drotation; a.dout[kOpacity] = dL_dopacity; a.dout[kColor] = dL_dcolor;
+    a.stage = static_cast<uint8_t*>(scratch); a.dflat = dflat; a.dplanes = dplanes;
+    GGD_CUDA_CHECK(cudaMemsetAsync(dflat, 0, sizeof(float) * a.L.flat_count, s));
+    if (dplanes) GGD_CUDA_CHECK(cudaMemsetAsync(dplanes, 0, sizeof(float) * 3 * (size_t)kFeat * cfg->plane_depth * cfg->plane_h * cfg->plane_w, s));
+    int dev = 0, sms = 0;
+    GGD_CUDA_CHECK(cudaGetDevice(&dev));
+    GGD_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (int e = launch_decode_bwd_chain(s, a, sms)) return e;
+    return launch_decode_bwd_dw(s, a.L, a.stage, (size_t)P, dflat, sms);
 }
 
 }  // extern "C"

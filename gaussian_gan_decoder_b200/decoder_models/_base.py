@@ -70,17 +70,18 @@ class FusedDecoderBase(nn.Module):
         return self.decode(synth["feature_planes"], init_position)
 
     # ---- fused path --------------------------------------------------------
-    def _cfg_for(self, planes):
+    def _cfg_for(self, planes, precision=None):
+        precision = precision or self.precision
         kw = self.G.rendering_kwargs
         depth = int(kw["triplane_depth"]) if "triplane_depth" in kw else 1
         arch = "panohead" if "triplane_depth" in kw else "eg3d"
-        key = (arch, depth, planes.shape[-2], planes.shape[-1], float(kw["box_warp"]), self.precision)
+        key = (arch, depth, planes.shape[-2], planes.shape[-1], float(kw["box_warp"]), precision)
         if key not in self._cfg_cache:
             if planes.shape[2] != 32 * depth:
                 raise ValueError(f"feature_planes has {planes.shape[2]} channels, expected 32*{depth}")
             self._cfg_cache[key] = fused.make_config(arch, self.VARIANT, depth, planes.shape[-2], planes.shape[-1],
                                                      10 if self.use_xyz_embedding else 0, self.hidden_dim,
-                                                     kw["box_warp"], self.SCALE_BIAS, self.precision)
+                                                     kw["box_warp"], self.SCALE_BIAS, precision)
         return self._cfg_cache[key]
 
     def _ensure_flat(self, planes):

@@ -100,6 +100,21 @@ class FlatParams:
         first = next(self._tensors(owner))[3]
         return self.flat is not None and first.data_ptr() == self.flat.data_ptr() and first.device == self.flat.device
 
+    def packed_weights_for(self, cfg):
+        """Packed copy for another kernel flavour (the backward always uses the fp32 pack)."""
+        if cfg.precision == self.cfg.precision:
+            return self.packed_weights()
+        ver = sum(t._version for t in self._params)
+        cache = getattr(self, "_alt_packed", None)
+        if cache is None or cache[0] != (cfg.precision, ver) or cache[1].device != self.flat.device:
+            lib = _lib.load()
+            _, n = param_counts(cfg)
+            buf = torch.empty(n, dtype=torch.float32, device=self.flat.device)
+            with torch.cuda.device(self.flat.device):
+                _lib.check(lib.ggd_decode_pack_weights(_stream(), C.byref(cfg), _lib.ptr(self.flat), _lib.ptr(buf)))
+            self._alt_packed = ((cfg.precision, ver), buf)
+        return self._alt_packed[1]
+
     def packed_weights(self):
         """Kernel-layout copy of the parameters, rebuilt only when the flat buffer changed."""
         # parameters are views of the flat buffer but carry their own version counters
@@ -141,24 +156,6 @@ def decode_forward(cfg, planes_nchw, xyz, packed, with_activations=True):
                                           p(out["color"]), p(act.get("act_scale")), p(act.get("act_rotation")),
                                           p(act.get("act_opacity"))))
     return {**out, **act}
-
-
-class _FusedDecode(torch.autograd.Function):
-    """Autograd boundary of the fused kernel.  Inputs that can require grad: the flat
-    parameter buffer and the feature planes (use_gen_finetune)."""
-
-    @staticmethod
-    def forward(ctx, owner, planes, xyz, flat):
-        res = decode_forward(owner._cfg_for(planes), planes, xyz, owner._flat.packed_weights())
-        owner._last_activated = {k: res[k] for k in ("act_scale", "act_rotation", "act_opacity")}
-        ctx.owner = owner
-        ctx.save_for_backward(planes, xyz)
-        return res["xyz"], res["scale"], res["rotation"], res["opacity"], res["color"]
-
-    @staticmethod
-    def backward(ctx, *grads):
-        from . import fused_backward
-        return fused_backward.backward(ctx, *grads)
 
 
 def single_head_forward(decoder, triplane_features, gaussian_features):

@@ -254,6 +254,30 @@ GGD_API int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, cons
                                float* out_opacity, float* out_color,
                                float* act_scale, float* act_rotation, float* act_opacity);
 
+/* Backward of ggd_decode_forward: gradients of the decoder parameters (flat
+ * nn.Linear layout, same offsets as ggd_decode_param_offset) and, optionally, of
+ * the feature planes in the generator's own layout [3][32*D][H][W] (what
+ * grid_sample backward scatters into; needed when use_gen_finetune trains G).
+ * Replaces PyTorch autograd through the reference decoder classes
+ * (main/decoder_models/base_decoder.py:21-27 x5, parallel_decoder.py:58-80 and
+ * the sequential variants) and grid_sample backward.  No gradient flows to
+ * init_position, as in the reference (it is an input).
+ *   planes_cl_f32 : fp32 channels-last planes (ggd_planes_channels_last, precision 0)
+ *   packed_f32    : ggd_decode_pack_weights output for precision 0
+ *   out_*         : the forward results (the chained variants feed them to later heads)
+ *   dL_d*         : gradients of the five results; any may be NULL (= zero)
+ *   scratch       : ggd_decode_backward_scratch_bytes(cfg, P) bytes of staging
+ *   dflat         : [flat_floats] overwritten;  dplanes: overwritten if non-NULL
+ * The backward recomputes the forward in fp32 whatever precision the forward ran in. */
+GGD_API size_t ggd_decode_backward_scratch_bytes(const ggd_decoder_config* cfg, int P);
+GGD_API int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl_f32,
+                                const float* xyz, int P, const float* flat_params, const float* packed_f32,
+                                const float* out_xyz, const float* out_scale, const float* out_rotation,
+                                const float* out_opacity, const float* out_color,
+                                const float* dL_dxyz, const float* dL_dscale, const float* dL_drotation,
+                                const float* dL_dopacity, const float* dL_dcolor,
+                                void* scratch, size_t scratch_bytes, float* dflat, float* dplanes);
+
 #ifdef __cplusplus
 }
 #endif

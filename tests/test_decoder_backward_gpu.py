@@ -1,0 +1,81 @@
+"""Decoder backward (chain kernel + tcgen05 weight-gradient GEMMs) against PyTorch autograd
+through the CPU oracle (= the reference's ATen ops).  Gradients are float sums with fp16-staged
+operands for the weight gradients: per tensor, max error <= 2e-2 of the tensor's max magnitude
+and 99 % of the elements within 3e-3 of it."""
+import os
+import sys
+
+import pytest
+import torch
+
+from _stubs import StubG
+from gaussian_gan_decoder_b200 import synthetic
+from gaussian_gan_decoder_b200.decoder_models import ParallelDecoder, SequentialDecoder, SequentialDecoderReverse
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+import decoder_oracle as do  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+CLASSES = {"parallel": ParallelDecoder, "sequential": SequentialDecoder, "sequential_reverse": SequentialDecoderReverse}
+HEADS = ("xyz", "scale", "rotation", "opacity", "color")
+
+
+def close(a, b, name, mx=2e-2, q=3e-3):
+    a, b = a.reshape(-1).double().cpu(), b.reshape(-1).double().cpu()
+    scale = b.abs().max().item() + 1e-30
+    err = (a - b).abs() / scale
+    assert err.max().item() <= mx, (name, err.max().item())
+    assert torch.quantile(err[:1_000_000], 0.99).item() <= q, (name, torch.quantile(err[:1_000_000], 0.99).item())
+
+
+@pytest.mark.parametrize("arch,variant,posenc,P,res", [("eg3d", "parallel", False, 1000, 32), ("panohead", "sequential_reverse", False, 777, 24),
+                                                         ("eg3d", "sequential", True, 300, 16), ("panohead", "parallel", False, 20_000, 64)])
+@pytest.mark.parametrize("precision", ["fp32", "fp16"])
+def test_gradients_match_autograd_of_the_oracle(cuda, arch, variant, posenc, P, res, precision):
+    g = synthetic.gen(23)
+    depth = 3 if arch == "panohead" else 1
+    planes = synthetic.planes(arch, g, res=res, depth=depth)
+    xyz = synthetic.head_shell_points(P, g) * 1.5
+    torch.manual_seed(11)
+    dec = CLASSES[variant](StubG(planes.to(cuda), arch, depth), use_xyz_embedding=posenc, use_gen_finetune=True, device=cuda)
+    dec.precision = precision
+    douts = {h: torch.randn(P, n, generator=g) for h, n in zip(HEADS, (3, 3, 4, 1, 3))}
+
+    # ours
+    pl = planes.to(cuda).requires_grad_(True)
+    out = dec.decode(pl, xyz.to(cuda))
+    loss = sum((out[h] * douts[h].to(cuda)).sum() for h in HEADS)
+    loss.backward()
+    ours = torch.cat([p.grad.reshape(-1) for p in dec.get_params_custom()[:40]]).cpu()
+    ours_planes = pl.grad.cpu()
+
+    # oracle + autograd on CPU
+    flat = torch.cat([p.detach().reshape(-1).cpu() for p in dec.get_params_custom()[:40]]).requires_grad_(True)
+    plr = planes.clone().requires_grad_(True)
+    ref = do.decode(arch, variant, 10 if posenc else 0, flat, plr, xyz, 1.0, depth)
+    sum((ref[h] * douts[h]).sum() for h in HEADS).backward()
+
+    layout, _ = do.flat_layout(variant, 10 if posenc else 0)
+    for h, l, kind, off, shape in layout:
+        n = 1
+        for d in shape:
+            n *= d
+        close(ours[off:off + n], flat.grad[off:off + n], f"{h}.{l}.{kind}")
+    close(ours_planes, plr.grad, "planes", mx=2e-2, q=3e-3)
+
+
+def test_flat_gradient_buffer_and_no_grad_path(cuda):
+    g = synthetic.gen(2)
+    planes = synthetic.planes("eg3d", g, res=16).to(cuda)
+    xyz = synthetic.head_shell_points(256, g).to(cuda)
+    dec = ParallelDecoder(StubG(planes), use_xyz_embedding=False, use_gen_finetune=False, device=cuda)
+    out = dec.decode(planes, xyz)
+    assert out.xyz.requires_grad
+    out.color.sum().backward()
+    grads = dec.get_params_custom()
+    assert all(p.grad is not None for p in grads)
+    # only the colour head (and nothing else) receives gradient from a colour-only loss
+    assert float(dec.color_decoder.backbone[6].bias.grad.abs().sum()) > 0
+    assert float(dec.xyz_decoder.backbone[0].weight.grad.abs().sum()) == 0
+    with torch.no_grad():
+        assert not dec.decode(planes, xyz).xyz.requires_grad
