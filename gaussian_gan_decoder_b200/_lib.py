@@ -63,6 +63,7 @@ SIGNATURES = {
     "ggd_decode_pack_weights": (_i, [_p, _cfg, _p, _p]),
     "ggd_planes_channels_last": (_i, [_p, _cfg, _p, _p]),
     "ggd_decode_forward": (_i, [_p, _cfg, _p, _p, _i, _p] + [_p] * 8),
+    "ggd_mlp_forward": (_i, [_p, _p, _p, _i, _i] + [_p] * 8 + [_i, _i, _p]),
     "ggd_decode_backward_scratch_bytes": (_sz, [_cfg, _i]),
     "ggd_decode_backward": (_i, [_p, _cfg, _p, _p, _i, _p, _p] + [_p] * 10 + [_p, _sz, _p, _p]),
 }

@@ -254,6 +254,15 @@ GGD_API int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, cons
                                float* out_opacity, float* out_color,
                                float* act_scale, float* act_rotation, float* act_opacity);
 
+/* One decoder head on caller-supplied features: mean over the three plane
+ * samples, concat with gaussian_features, Linear-GELU x3, Linear.  Replaces
+ * Decoder.forward(triplane_features[3][P][32], gaussian_features[P][k]) ->
+ * [P][out] (main/decoder_models/base_decoder.py:21-27) when that module is called
+ * on its own; weights are the nn.Linear tensors themselves (W[out][in]). */
+GGD_API int ggd_mlp_forward(void* stream, const float* tri_features, const float* gaussian_features, int k, int P,
+                            const float* W0, const float* b0, const float* W1, const float* b1, const float* W2,
+                            const float* b2, const float* W3, const float* b3, int hidden, int out_features, float* out);
+
 /* Backward of ggd_decode_forward: gradients of the decoder parameters (flat
  * nn.Linear layout, same offsets as ggd_decode_param_offset) and, optionally, of
  * the feature planes in the generator's own layout [3][32*D][H][W] (what

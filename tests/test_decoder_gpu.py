@@ -117,3 +117,19 @@ def test_precision_switch_gives_consistent_results(cuda):
     for h in HEADS:
         assert torch.equal(outs["fp16"][0][h], outs["fp16"][1][h])          # deterministic
         assert (outs["fp16"][0][h] - outs["fp32"][0][h]).abs().max().item() <= 5e-4
+
+
+def test_standalone_decoder_forward(cuda):
+    """Decoder.forward(triplane_features[3,P,32], gaussian_features[P,k]) -> [P,out] (reference signature)."""
+    from gaussian_gan_decoder_b200.decoder_models import Decoder
+    torch.manual_seed(3)
+    for k, out in ((3, 3), (14, 4), (63, 1)):
+        d = Decoder(n_features=32 + k, out_features=out).to(cuda)
+        tri, gf = torch.randn(3, 1000, 32, device=cuda), torch.randn(1000, k, device=cuda)
+        with torch.no_grad():
+            got = d(tri, gf)
+            ref = d.backbone(torch.cat([tri.mean(0), gf], -1))
+        assert got.shape == (1000, out)
+        assert (got - ref).abs().max().item() <= 1e-4
+    with pytest.raises(NotImplementedError):
+        d(tri, gf)     # grad-enabled call: inference-only, fails loudly
