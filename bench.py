@@ -279,6 +279,102 @@ def run_reference(args):
     }
 
 
+def run_extra(args, rank, world, dev):
+    """Secondary workloads (reported in DESIGN.md / profiles/, not the driver's headline):
+    train  = BASELINE configs[3]: decoder training step (decode + raster, fwd + bwd, Adam, grad all-reduce)
+    views  = BASELINE configs[2]: 64 latents x 8 views at 512^2, latent-major sharding over the ranks
+    hires  = BASELINE configs[4]: 2048^2 raster of 2M trained-like Gaussians (sort / blend bound)"""
+    from gaussian_gan_decoder_b200 import synthetic
+    from gaussian_gan_decoder_b200.data_parallel import shard_frames
+    from gaussian_gan_decoder_b200.pipeline import FramePipeline
+    from gaussian_gan_decoder_b200.training import training_step
+    torch.cuda.set_device(dev)
+    bg = torch.tensor(synthetic.BG[ARCH], dtype=torch.float32, device=dev)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    extra = {}
+    if args.workload == "train":
+        sets = [(pl.to(dev), xyz.to(dev)) for pl, xyz in make_inputs(rank, dev)]
+        dec = make_decoder(sets[0][0], dev)
+        cam = device_camera(dev)
+        opt = torch.optim.Adam(dec.get_params_custom(), lr=9e-5)
+        z, c = torch.zeros(1, 512, device=dev), torch.zeros(1, 25, device=dev)
+        g = synthetic.gen(99 + rank)
+        dimg = torch.randn(3, SIZE, SIZE, generator=g).to(dev)
+
+        def step(i):
+            dec.G.planes = sets[i % len(sets)][0]
+            training_step(dec, opt, z, c, sets[i % len(sets)][1], cam, None, bg, dL_dimage=dimg)
+
+        units, name = 1, "decoder training steps/s (decode+raster fwd+bwd, Adam, grad all-reduce), 500k Gaussians @512^2"
+    elif args.workload == "views":
+        pairs = shard_frames(64, 8, rank, world, "latent")
+        lat = sorted({l for l, _ in pairs})
+        planes = {l: synthetic.planes("eg3d", synthetic.gen(1000 + l), res=256).to(dev) for l in lat[:4]}   # 4 distinct plane sets, reused
+        xyz = synthetic.head_shell_points(P_FULL, synthetic.gen(7)).to(dev)
+        from gaussian_gan_decoder_b200.decoder_models import ParallelDecoder
+        torch.manual_seed(303)
+        dec = ParallelDecoder(synthetic.SyntheticGenerator(planes[lat[0]], "eg3d", 1), use_xyz_embedding=False, use_gen_finetune=False, device=dev)
+        cams = []
+        for v in range(8):
+            cam = synthetic.camera(SIZE, FOV, h=math.pi / 2 + 0.25 * (v - 3.5))
+            for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+                setattr(cam, k, getattr(cam, k).contiguous().to(dev))
+            cams.append(cam)
+        pipe = FramePipeline(dec, P_FULL, SIZE, dev)
+
+        def step(i):   # one step = this rank's whole share: decode each latent once, render its 8 views
+            for l in lat:
+                pl = planes[lat[(lat.index(l)) % len(planes)] if l not in planes else l]
+                pipe.frame(pl, xyz, cams[0], bg)
+                for v in range(1, 8):
+                    pipe.render_only(cams[v], bg)
+            pipe.check()
+
+        units, name = len(pairs), "frames/s over 64 latents x 8 views @512^2 (EG3D planes, ParallelDecoder), latent-major shards"
+    else:   # hires
+        P5, S5 = 2_000_000, 2048
+        sc = synthetic.raster_scene(P5, size=S5, fov_deg=FOV, seed_offset=50 + rank, device=dev)
+        from gaussian_gan_decoder_b200 import rasterizer as rz
+        e = torch.empty(0, device=dev)
+
+        def step(i):
+            return rz._C.rasterize_gaussians(sc["bg"], sc["means3D"], e, sc["opacities"], sc["scales"], sc["rotations"], 1.0, e,
+                                            sc["viewmatrix"], sc["projmatrix"], sc["tanfovx"], sc["tanfovy"], S5, S5, sc["shs"], 0,
+                                            sc["campos"], False, False)[0]
+
+        extra["num_rendered"] = step(0)
+        units, name = 1, "rasterised frames/s @2048^2, 2M trained-like Gaussians (raster only)"
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ms = float(t[0])
+        total_units = torch.tensor([units], device=dev, dtype=torch.float64)
+        torch.distributed.all_reduce(total_units)
+        units_all = float(total_units[0])
+    else:
+        units_all = units
+    if rank == 0:
+        print(json.dumps({"metric": name, "value": round(units_all * args.steps / (ms * 1e-3), 3), "unit": "1/s", "n_gpus": world,
+                          "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4),
+                          "higher_is_better": True, "scaling": "weak" if args.workload != "views" else "strong",
+                          "data": "synthetic", "config": {"workload": args.workload, **extra}}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -286,6 +382,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="frame", choices=["frame", "train", "views", "hires"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -302,6 +399,12 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.distributed.init_process_group("nccl", device_id=dev)
+    if args.workload != "frame":
+        run_extra(args, rank, world, dev)
+        if world > 1:
+            torch.distributed.barrier()
+            torch.distributed.destroy_process_group()
+        return
     res = run_ours(args, rank, world, dev)
     if rank == 0:
         line = res[0]

@@ -66,6 +66,21 @@ class FramePipeline:
             C.c_void_p(self.pinned.data_ptr())))
         return self.image
 
+    def render_only(self, cam, bg):
+        """Another view of the attributes decoded by the last ``frame()`` (decoded attributes depend
+        on the latent only): rasterise again with a different camera."""
+        import math
+        lib, p, P = self.lib, _lib.ptr, self.P
+        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _lib.check(lib.ggd_raster_forward(
+            s, P, 0, 1, p(bg), self.W, self.H, p(self.out["xyz"]), p(self.out["color"]), None,
+            p(self.act["opacity"]), p(self.act["scale"]), 1.0, p(self.act["rotation"]), None,
+            p(cam.world_view_transform), p(cam.full_proj_transform), p(cam.camera_center),
+            math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), 0,
+            p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
+            C.c_void_p(self.pinned.data_ptr())))
+        return self.image
+
     def check(self):
         """Synchronise and verify the last frame fit the binning buffer; grows it otherwise.
         Returns (num_rendered, overflowed)."""
