@@ -245,14 +245,26 @@ onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ key
         atomicExch(my_lb, kLbPre | count);
     } else {
         atomicExch(my_lb, kLbAgg | count);
+        // windowed look-back: kWin predecessor words are fetched as independent loads per round, so the
+        // walk costs one L2 round trip per kWin tiles instead of one per tile
+        constexpr int kWin = 8;
         int look = (int)tile - 1;
-        while (true) {
-            const uint32_t w = *reinterpret_cast<volatile uint32_t*>(lookback + (size_t)look * kRadixBins + t);
-            const uint32_t f = w >> 30;
-            if (f == 0) continue;
-            excl += w & kLbMask;
-            if (f == 2) break;
-            --look;
+        bool found = false;
+        while (!found) {
+            uint32_t w[kWin];
+#pragma unroll
+            for (int i = 0; i < kWin; ++i)
+                w[i] = (look - i >= 0) ? *reinterpret_cast<volatile uint32_t*>(lookback + (size_t)(look - i) * kRadixBins + t)
+                                       : (2u << 30);      // virtual inclusive prefix 0 in front of tile 0
+#pragma unroll
+            for (int i = 0; i < kWin; ++i) {
+                if (found) break;
+                const uint32_t f = w[i] >> 30;
+                if (f == 0) break;                        // not published yet: re-read from here
+                excl += w[i] & kLbMask;
+                --look;
+                if (f == 2) found = true;
+            }
         }
         atomicExch(my_lb, kLbPre | (excl + count));
     }

@@ -77,28 +77,54 @@ __global__ void pack_weights_kernel(const DecoderLayout L, const float* __restri
 }
 
 // ---- planes: reference NCHW [3][C*D][H][W] (channel = c*D + d) -> [3][D][H][W][C] ----
-// One CTA transposes a [C=32][32 texels] slab through shared memory: reads are
-// contiguous along W, writes are contiguous 128-byte texel records.
+// One CTA transposes a [C=32][128 texels] slab through shared memory: reads are 16-byte vectors
+// contiguous along W, writes are whole texel records (128 B fp32 / 64 B fp16), 16 bytes per thread.
+constexpr int kSlab = 128;
 template <typename TOut>
 __global__ void __launch_bounds__(256)
 planes_channels_last_kernel(const float* __restrict__ src, TOut* __restrict__ dst, int D, int H, int W)
 {
-    __shared__ float tile[kFeat][33];
+    __shared__ float tile[kFeat][kSlab + 4];
     const size_t HW = (size_t)H * W;
-    const size_t slabs_per_pd = (HW + 31) / 32;
+    const size_t slabs_per_pd = (HW + kSlab - 1) / kSlab;
     const size_t slab = blockIdx.x;
     const int pd = (int)(slab / slabs_per_pd);          // plane * D + d
-    const size_t t0 = (slab % slabs_per_pd) * 32;       // first texel of the slab
+    const size_t t0 = (slab % slabs_per_pd) * kSlab;    // first texel of the slab
     const int plane = pd / D, d = pd % D;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-    for (int c = ty; c < kFeat; c += 8) {
-        const size_t t = t0 + tx;
-        tile[c][tx] = t < HW ? __ldg(src + ((size_t)plane * kFeat * D + (size_t)c * D + d) * HW + t) : 0.f;
+    const bool vec = (HW % 4 == 0);
+    for (int i = threadIdx.x; i < kFeat * (kSlab / 4); i += 256) {
+        const int c = i / (kSlab / 4), q = i % (kSlab / 4);
+        const size_t t = t0 + 4 * q;
+        const float* p = src + ((size_t)plane * kFeat * D + (size_t)c * D + d) * HW + t;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (vec && t + 3 < HW) v = __ldg(reinterpret_cast<const float4*>(p));
+        else {
+            if (t < HW) v.x = __ldg(p);
+            if (t + 1 < HW) v.y = __ldg(p + 1);
+            if (t + 2 < HW) v.z = __ldg(p + 2);
+            if (t + 3 < HW) v.w = __ldg(p + 3);
+        }
+        tile[c][4 * q] = v.x; tile[c][4 * q + 1] = v.y; tile[c][4 * q + 2] = v.z; tile[c][4 * q + 3] = v.w;
     }
     __syncthreads();
-    for (int tt = ty; tt < 32; tt += 8) {
+    constexpr int kPer = 16 / sizeof(TOut);              // channels per 16-byte store: 4 (fp32) or 8 (fp16)
+    constexpr int kChunks = kFeat / kPer;
+    for (int i = threadIdx.x; i < kSlab * kChunks; i += 256) {
+        const int tt = i / kChunks, ch = (i % kChunks) * kPer;
         const size_t t = t0 + tt;
-        if (t < HW) dst[(((size_t)plane * D + d) * HW + t) * kFeat + tx] = static_cast<TOut>(tile[tx][tt]);
+        if (t >= HW) continue;
+        TOut* o = dst + (((size_t)plane * D + d) * HW + t) * kFeat + ch;
+        if constexpr (sizeof(TOut) == 4) {
+            *reinterpret_cast<float4*>(o) = make_float4(tile[ch][tt], tile[ch + 1][tt], tile[ch + 2][tt], tile[ch + 3][tt]);
+        } else {
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const __half2 h = __floats2half2_rn(tile[ch + 2 * e][tt], tile[ch + 2 * e + 1][tt]);
+                pk[e] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            *reinterpret_cast<uint4*>(o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
     }
 }
 
@@ -113,7 +139,7 @@ int launch_pack_weights(cudaStream_t s, const DecoderLayout& L, const float* fla
 
 int launch_planes_channels_last(cudaStream_t s, const float* src, void* dst, int D, int H, int W, bool half_out)
 {
-    const size_t slabs = (size_t)3 * D * (((size_t)H * W + 31) / 32);
+    const size_t slabs = (size_t)3 * D * (((size_t)H * W + kSlab - 1) / kSlab);
     if (half_out) planes_channels_last_kernel<__half><<<(unsigned)slabs, 256, 0, s>>>(src, static_cast<__half*>(dst), D, H, W);
     else planes_channels_last_kernel<float><<<(unsigned)slabs, 256, 0, s>>>(src, static_cast<float*>(dst), D, H, W);
     GGD_LAUNCH_CHECK("planes_channels_last_kernel");

@@ -127,18 +127,20 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                         ++n_acc;
                         ptx::tc_fence_after();
                         if (l < kLayers - 1) {
-#pragma unroll 1
-                            for (int c = colhalf * 2; c < colhalf * 2 + 2; ++c) {
-                                uint32_t v[32];
-                                ptx::tmem_ld32(trow + c * 32, v);
-                                ptx::tmem_ld_wait();
+                            uint32_t v2[2][32];
+                            ptx::tmem_ld32(trow + colhalf * 64, v2[0]);
+                            ptx::tmem_ld32(trow + colhalf * 64 + 32, v2[1]);
+                            ptx::tmem_ld_wait();
+#pragma unroll
+                            for (int cc = 0; cc < 2; ++cc) {
+                                const int c = colhalf * 2 + cc;
 #pragma unroll
                                 for (int j = 0; j < 4; ++j) {
                                     uint32_t o[4];
 #pragma unroll
                                     for (int q = 0; q < 4; ++q) {
-                                        const __half2 y = gelu_h2(__floats2half2_rn(__uint_as_float(v[8 * j + 2 * q]),
-                                                                                     __uint_as_float(v[8 * j + 2 * q + 1])));
+                                        const __half2 y = gelu_h2(__floats2half2_rn(__uint_as_float(v2[cc][8 * j + 2 * q]),
+                                                                                     __uint_as_float(v2[cc][8 * j + 2 * q + 1])));
                                         o[q] = *reinterpret_cast<const uint32_t*>(&y);
                                     }
                                     *reinterpret_cast<uint4*>(A + canon(r, c * 32 + 8 * j, kKH)) = make_uint4(o[0], o[1], o[2], o[3]);
