@@ -5,12 +5,12 @@
 // Embedder, 5 x Decoder, head post-math, GaussianModel activations).
 //
 // Structure (one persistent CTA per SM, 18 warps):
-//   warps 0-7 / 8-15 two epilogue groups of 8 warps; thread = one point (TMEM lane) x one half
-//                    of the 128 accumulator columns.  They sample the planes into the layer-0
-//                    operand, turn accumulators into the next layer's fp16 operand (GELU in
-//                    half2 with MUFU tanh) and apply the head post-math.  The two groups work
-//                    on alternate 128-point tiles so one group's epilogue overlaps the other
-//                    group's MMAs.
+//   warps 0-15       epilogue: thread = one point (TMEM lane) x one quarter of the 128 accumulator
+//                    columns.  They sample the planes into the layer-0 operands, turn an
+//                    accumulator into the next layer's fp16 operand (GELU in half2 with MUFU
+//                    tanh) and apply the head post-math.  Two 128-point tiles ("slots", each with
+//                    its own operand buffer and TMEM accumulator) are in flight: while all 16
+//                    warps convert slot A, the tensor core runs slot B's MMAs, and vice versa.
 //   warp 16          one thread issues tcgen05.mma (M=128, N=128 or 16, K=16 per instruction)
 //   warp 17          one thread streams the packed fp16 weights of the current head, layer by
 //                    layer, with 1-D bulk async copies into four shared-memory slots; a slot

@@ -35,7 +35,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
 
     if (tid == 0) {
         for (int i = 0; i < 8; ++i) ptx::mbar_init(&bars[i], 1);
-        ptx::mbar_init(&bars[B_AREADY], 256); ptx::mbar_init(&bars[B_AREADY + 1], 256);
+        ptx::mbar_init(&bars[B_AREADY], 16); ptx::mbar_init(&bars[B_AREADY + 1], 16);   // one arrival per epilogue warp
         ptx::mbar_init(&bars[B_ACCFULL], 1); ptx::mbar_init(&bars[B_ACCFULL + 1], 1);
         ptx::mbar_fence_init();
     }
@@ -49,53 +49,51 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
     const int groups = (a.P + pts_per_group - 1) / pts_per_group;
 
     if (warp < 16) {
-        // ====================== epilogue / sampling: 8 warps per ping-pong slot ======================
-        // Two warps share every TMEM lane quarter and split the 128 accumulator columns in halves.
-        const int wg = warp >> 3, e = tid & 255, r = e & 127, colhalf = e >> 7;
-        uint8_t* A = smem + sm.a[wg];
-        const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)wg * 256;
-        if (colhalf == 0) {   // constant bias-column block of the hidden operand: k = 128 is 1, k = 129..143 are 0
+        // ============ epilogue / sampling: all 16 warps work on whichever slot's accumulator is ready ============
+        // Four warps share every TMEM lane quarter and split the 128 accumulator columns in quarters, so a
+        // tile-layer epilogue is short; while they convert slot A the tensor core runs slot B's MMAs.
+        const int e = tid, r = e & 127, colq = e >> 7;          // row (point) and 32-column block of this thread
+        const uint32_t trow0 = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        if (colq == 0) {   // constant bias-column block of both hidden operands: k = 128 is 1, k = 129..143 are 0
             const uint4 one = make_uint4(0x00003c00u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);
-            *reinterpret_cast<uint4*>(A + canon(r, kHidden, kKH)) = one;
-            *reinterpret_cast<uint4*>(A + canon(r, kHidden + 8, kKH)) = zero;
+            for (int w2 = 0; w2 < 2; ++w2) {
+                *reinterpret_cast<uint4*>(smem + sm.a[w2] + canon(r, kHidden, kKH)) = one;
+                *reinterpret_cast<uint4*>(smem + sm.a[w2] + canon(r, kHidden + 8, kKH)) = zero;
+            }
         }
         const size_t plane_stride = (size_t)a.D * a.H * a.W * kFeat;
-        uint32_t n_acc = 0;
-        const int my_tiles = (T - wg + 1) / 2;          // tiles wg, wg+2, ...
+        uint32_t n_acc[2] = {0, 0};
         for (int g = blockIdx.x; g < groups; g += gridDim.x) {
-            // ---- sample my tiles into their layer-0 operands ----
-            for (int i = wg; i < T; i += 2) {
+            // ---- sample all T tiles into their layer-0 operands: 4 lanes per point, 128 points per pass ----
+            for (int i = 0; i < T; ++i) {
                 uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
                 const int p0 = (g * T + i) * kM;
-                const int sub = e & 3, grp = e >> 2;        // 4 lanes per point, 8 channels per lane
+                const int sub = e & 3, pt = e >> 2, gps = p0 + pt;
                 const __half* pl = reinterpret_cast<const __half*>(a.planes);
-                for (int it = 0; it < kM / 64; ++it) {
-                    const int pt = it * 64 + grp, gp = p0 + pt;
-                    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                    if (gp < a.P) {
-                        const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp);
-                        const float y = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 1);
-                        const float z = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 2);
-                        if (a.arch == 0) {   // (x,y) (x,z) (z,x)
-                            sample8h<1>(pl, 1, a.H, a.W, x, y, 0.f, sub, acc);
-                            sample8h<1>(pl + plane_stride, 1, a.H, a.W, x, z, 0.f, sub, acc);
-                            sample8h<1>(pl + 2 * plane_stride, 1, a.H, a.W, z, x, 0.f, sub, acc);
-                        } else {             // (x,y,z) (x,z,y) (y,z,x) -> (W,H,D)
-                            sample8h<2>(pl, a.D, a.H, a.W, x, y, z, sub, acc);
-                            sample8h<2>(pl + plane_stride, a.D, a.H, a.W, x, z, y, sub, acc);
-                            sample8h<2>(pl + 2 * plane_stride, a.D, a.H, a.W, y, z, x, sub, acc);
-                        }
+                float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                if (gps < a.P) {
+                    const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps);
+                    const float y = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps + 1);
+                    const float z = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps + 2);
+                    if (a.arch == 0) {   // (x,y) (x,z) (z,x)
+                        sample8h<1>(pl, 1, a.H, a.W, x, y, 0.f, sub, acc);
+                        sample8h<1>(pl + plane_stride, 1, a.H, a.W, x, z, 0.f, sub, acc);
+                        sample8h<1>(pl + 2 * plane_stride, 1, a.H, a.W, z, x, 0.f, sub, acc);
+                    } else {             // (x,y,z) (x,z,y) (y,z,x) -> (W,H,D)
+                        sample8h<2>(pl, a.D, a.H, a.W, x, y, z, sub, acc);
+                        sample8h<2>(pl + plane_stride, a.D, a.H, a.W, x, z, y, sub, acc);
+                        sample8h<2>(pl + 2 * plane_stride, a.D, a.H, a.W, y, z, x, sub, acc);
                     }
-                    uint32_t pk[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const __half2 hv = __floats2half2_rn(acc[2 * q] / 3.f, acc[2 * q + 1] / 3.f);
-                        pk[q] = *reinterpret_cast<const uint32_t*>(&hv);
-                    }
-                    *reinterpret_cast<uint4*>(base + canon(pt, 8 * sub, k0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 }
+                uint32_t pk[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const __half2 hv = __floats2half2_rn(acc[2 * q] / 3.f, acc[2 * q + 1] / 3.f);
+                    pk[q] = *reinterpret_cast<const uint32_t*>(&hv);
+                }
+                *reinterpret_cast<uint4*>(base + canon(pt, 8 * sub, k0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 // row-wise part: position (+ embedding), zeroed chain columns, constant one
-                if (colhalf != 0) continue;
+                if (colq != 0) continue;
                 const int gp = p0 + r;
                 float px[3] = {0.f, 0.f, 0.f};
                 if (gp < a.P) for (int j = 0; j < 3; ++j) px[j] = __ldg(a.xyz + 3 * (size_t)gp + j);
@@ -111,68 +109,76 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                 for (int k = kFeat + L.pos_dim; k < k0 - 1; ++k) put(k, 0.f);
                 put(k0 - 1, 1.0f);
             }
+            // 512 arrivals on one shared-memory word would serialise: every thread fences its own writes,
+            // the warp converges, one lane arrives
             ptx::fence_proxy_async();
-            ptx::mbar_arrive(&bars[B_AREADY + wg]);
+            __syncwarp();
+            if (lane == 0) {
+                ptx::mbar_arrive(&bars[B_AREADY]);
+                if (T > 1) ptx::mbar_arrive(&bars[B_AREADY + 1]);
+            }
 
             int chain_col = kFeat + L.pos_dim;
             for (int hi = 0; hi < kHeads; ++hi) {
                 const int h = L.order[hi];
                 const int n_out = head_out(h);
-                for (int ti = 0; ti < my_tiles; ++ti) {
-                    const int i = wg + 2 * ti;
-                    uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
-                    const int gp = (g * T + i) * kM + r;
+                for (int p = 0; p < (T + 1) / 2; ++p) {
                     for (int l = 0; l < kLayers; ++l) {
-                        ptx::mbar_wait(&bars[B_ACCFULL + wg], n_acc & 1);
-                        ++n_acc;
-                        ptx::tc_fence_after();
-                        if (l < kLayers - 1) {
-                            uint32_t v2[2][32];
-                            ptx::tmem_ld32(trow + colhalf * 64, v2[0]);
-                            ptx::tmem_ld32(trow + colhalf * 64 + 32, v2[1]);
-                            ptx::tmem_ld_wait();
-#pragma unroll
-                            for (int cc = 0; cc < 2; ++cc) {
-                                const int c = colhalf * 2 + cc;
+                        for (int wg = 0; wg < 2; ++wg) {
+                            const int i = 2 * p + wg;
+                            if (i >= T) continue;
+                            uint8_t* A = smem + sm.a[wg];
+                            uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
+                            const uint32_t trow = trow0 + (uint32_t)wg * 256;
+                            const int gp = (g * T + i) * kM + r;
+                            if (lane == 0) ptx::mbar_wait(&bars[B_ACCFULL + wg], n_acc[wg] & 1);   // one poller per warp
+                            __syncwarp();
+                            ++n_acc[wg];
+                            ptx::tc_fence_after();
+                            if (l < kLayers - 1) {
+                                uint32_t v[32];
+                                ptx::tmem_ld32(trow + colq * 32, v);
+                                ptx::tmem_ld_wait();
 #pragma unroll
                                 for (int j = 0; j < 4; ++j) {
                                     uint32_t o[4];
 #pragma unroll
                                     for (int q = 0; q < 4; ++q) {
-                                        const __half2 y = gelu_h2(__floats2half2_rn(__uint_as_float(v2[cc][8 * j + 2 * q]),
-                                                                                     __uint_as_float(v2[cc][8 * j + 2 * q + 1])));
+                                        const __half2 y = gelu_h2(__floats2half2_rn(__uint_as_float(v[8 * j + 2 * q]),
+                                                                                     __uint_as_float(v[8 * j + 2 * q + 1])));
                                         o[q] = *reinterpret_cast<const uint32_t*>(&y);
                                     }
-                                    *reinterpret_cast<uint4*>(A + canon(r, c * 32 + 8 * j, kKH)) = make_uint4(o[0], o[1], o[2], o[3]);
+                                    *reinterpret_cast<uint4*>(A + canon(r, colq * 32 + 8 * j, kKH)) = make_uint4(o[0], o[1], o[2], o[3]);
                                 }
-                            }
-                        } else if (colhalf == 0) {
-                            uint32_t v[4];
-                            ptx::tmem_ld4(trow + kHidden, v);
-                            ptx::tmem_ld_wait();
-                            float o[4] = {__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3])};
-                            if (h == kXyz) {
-                                for (int j = 0; j < 3; ++j) o[j] = o[j] * 0.01f + (gp < a.P ? __ldg(a.xyz + 3 * (size_t)gp + j) : 0.f);
-                            }
-                            if (h == kScale) for (int j = 0; j < 3; ++j) o[j] = -softplus_f(o[j] + 5.0f) + a.scale_bias;
-                            if (gp < a.P) {
-                                for (int j = 0; j < n_out; ++j) a.out[h][(size_t)gp * n_out + j] = o[j];
-                                if (h == kScale && a.act_scale) for (int j = 0; j < 3; ++j) a.act_scale[(size_t)gp * 3 + j] = expf(o[j]);
-                                if (h == kOpacity && a.act_opacity) a.act_opacity[gp] = 1.0f / (1.0f + expf(-o[0]));
-                                if (h == kRot && a.act_rot) {
-                                    const float nrm = fmaxf(sqrtf(o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3]), 1e-12f);
-                                    for (int j = 0; j < 4; ++j) a.act_rot[(size_t)gp * 4 + j] = o[j] / nrm;
+                            } else if (colq == 0) {
+                                uint32_t v[4];
+                                ptx::tmem_ld4(trow + kHidden, v);
+                                ptx::tmem_ld_wait();
+                                float o[4] = {__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3])};
+                                if (h == kXyz) {
+                                    for (int j = 0; j < 3; ++j) o[j] = o[j] * 0.01f + (gp < a.P ? __ldg(a.xyz + 3 * (size_t)gp + j) : 0.f);
                                 }
+                                if (h == kScale) for (int j = 0; j < 3; ++j) o[j] = -softplus_f(o[j] + 5.0f) + a.scale_bias;
+                                if (gp < a.P) {
+                                    for (int j = 0; j < n_out; ++j) a.out[h][(size_t)gp * n_out + j] = o[j];
+                                    if (h == kScale && a.act_scale) for (int j = 0; j < 3; ++j) a.act_scale[(size_t)gp * 3 + j] = expf(o[j]);
+                                    if (h == kOpacity && a.act_opacity) a.act_opacity[gp] = 1.0f / (1.0f + expf(-o[0]));
+                                    if (h == kRot && a.act_rot) {
+                                        const float nrm = fmaxf(sqrtf(o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3]), 1e-12f);
+                                        for (int j = 0; j < 4; ++j) a.act_rot[(size_t)gp * 4 + j] = o[j] / nrm;
+                                    }
+                                }
+                                if (L.variant != 0 && hi < kHeads - 1)
+                                    for (int j = 0; j < n_out; ++j)
+                                        *reinterpret_cast<__half*>(base + canon(r, chain_col + j, k0)) = __float2half_rn(o[j]);
                             }
-                            if (L.variant != 0 && hi < kHeads - 1)
-                                for (int j = 0; j < n_out; ++j)
-                                    *reinterpret_cast<__half*>(base + canon(r, chain_col + j, k0)) = __float2half_rn(o[j]);
-                        }
-                        const bool last_of_group = (hi == kHeads - 1) && (ti == my_tiles - 1) && (l == kLayers - 1);
-                        ptx::tc_fence_before();
-                        if (!last_of_group) {
-                            ptx::fence_proxy_async();
-                            ptx::mbar_arrive(&bars[B_AREADY + wg]);
+                            const bool last_of_group = (hi == kHeads - 1) && (i + 2 >= T) && (l == kLayers - 1);
+                            ptx::tc_fence_before();
+                            if (!last_of_group) {
+                                ptx::fence_proxy_async();
+                                __syncwarp();
+                                if (lane == 0) ptx::mbar_arrive(&bars[B_AREADY + wg]);
+                            }
                         }
                     }
                 }
