@@ -39,6 +39,60 @@ class GaussianModel:
             g._activated = (activated["act_scale"], activated["act_rotation"], activated["act_opacity"])
         return g
 
+    # ---- the reference's .ply wire format (gaussian_splatting/scene/gaussian_model.py:259-303) ----
+    def construct_list_of_attributes(self):
+        l = ['x', 'y', 'z', 'nx', 'ny', 'nz']
+        l += [f'f_dc_{i}' for i in range(self._features_dc.shape[1] * self._features_dc.shape[2])]
+        if self.active_sh_degree > 0:
+            l += [f'f_rest_{i}' for i in range(self._features_rest.shape[1] * self._features_rest.shape[2])]
+        l.append('opacity')
+        l += [f'scale_{i}' for i in range(self._scaling.shape[1])]
+        l += [f'rot_{i}' for i in range(self._rotation.shape[1])]
+        return l
+
+    def save_ply(self, path):
+        """Binary little-endian PLY with the reference's property names and order (what the external
+        viewers load).  Written directly; no plyfile dependency."""
+        import os
+        import numpy as np
+        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+        cols = [self._xyz.detach().cpu().numpy(), np.zeros((self._xyz.shape[0], 3), np.float32),
+                self._features_dc.detach().transpose(1, 2).flatten(start_dim=1).contiguous().cpu().numpy()]
+        if self.active_sh_degree > 0:
+            cols.append(self._features_rest.detach().transpose(1, 2).flatten(start_dim=1).contiguous().cpu().numpy())
+        cols += [self._opacity.detach().cpu().numpy(), self._scaling.detach().cpu().numpy(),
+                 self._rotation.detach().cpu().numpy()]
+        data = np.ascontiguousarray(np.concatenate(cols, axis=1), dtype='<f4')
+        names = self.construct_list_of_attributes()
+        assert data.shape[1] == len(names)
+        header = "ply\nformat binary_little_endian 1.0\nelement vertex %d\n" % data.shape[0]
+        header += "".join(f"property float {n}\n" for n in names) + "end_header\n"
+        with open(path, "wb") as f:
+            f.write(header.encode("ascii"))
+            f.write(data.tobytes())
+
+    def load_ply(self, path, device="cpu"):
+        import numpy as np
+        with open(path, "rb") as f:
+            names, n = [], 0
+            while True:
+                line = f.readline().decode("ascii").strip()
+                if line.startswith("element vertex"):
+                    n = int(line.split()[-1])
+                elif line.startswith("property float"):
+                    names.append(line.split()[-1])
+                elif line == "end_header":
+                    break
+            data = np.frombuffer(f.read(n * len(names) * 4), dtype='<f4').reshape(n, len(names))
+        col = lambda prefix: torch.from_numpy(np.stack([data[:, names.index(k)] for k in names if k.startswith(prefix)], 1).copy())
+        self._xyz = torch.from_numpy(data[:, :3].copy()).to(device)
+        self._features_dc = col("f_dc_").view(n, 3, -1).transpose(1, 2).contiguous().to(device)
+        self._opacity = col("opacity").to(device)
+        self._scaling = col("scale_").to(device)
+        self._rotation = col("rot_").to(device)
+        self._activated = None
+        return self
+
     @property
     def get_scaling(self):
         return self._activated[0] if self._activated is not None else torch.exp(self._scaling)

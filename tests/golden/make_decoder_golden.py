@@ -97,6 +97,10 @@ def run_arch(arch):
         for h in HEADS:
             z["out_" + h] = out[h].numpy()
         np.savez_compressed(os.path.join(HERE, f"decoder_{name}.npz"), **z)
+        import json
+        keys = {k: list(v.shape) for k, v in dec.state_dict().items() if not k.startswith("G.")}
+        with open(os.path.join(HERE, f"state_dict_keys_{name}.json"), "w") as f:
+            json.dump(keys, f, indent=0)
         print(name, "flat params", flat.numel(), {h: tuple(out[h].shape) for h in HEADS})
 
 
