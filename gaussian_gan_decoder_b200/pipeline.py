@@ -66,6 +66,19 @@ class FramePipeline:
             C.c_void_p(self.pinned.data_ptr())))
         return self.image
 
+    def capture(self, planes_nchw, xyz, cam, bg):
+        """Record one frame (planes -> decode -> rasterise) into a CUDA graph.  The graph reads the given
+        tensors in place: refill them (``copy_``) and call ``replay()``.  Run ``frame()`` + ``check()``
+        once before capturing so the binning capacity is settled and the weights are packed."""
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self.frame(planes_nchw, xyz, cam, bg)
+        return self._graph
+
+    def replay(self):
+        self._graph.replay()
+        return self.image
+
     def render_only(self, cam, bg):
         """Another view of the attributes decoded by the last ``frame()`` (decoded attributes depend
         on the latent only): rasterise again with a different camera."""
