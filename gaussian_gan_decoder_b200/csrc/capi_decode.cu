@@ -96,7 +96,9 @@ size_t ggd_decode_backward_scratch_bytes(const ggd_decoder_config* cfg, int P)
 {
     DecoderLayout L;
     if (check_cfg(cfg, &L) || P <= 0) return 0;
-    return bwd_stage(L.pos_dim, (size_t)P).bytes;
+    const size_t simt = bwd_stage(L.pos_dim, (size_t)P).bytes;
+    const size_t tc = align_up(bwd_stage_tc((size_t)P).bytes, 256) + align_up(tc_packed_bytes(L), 256) + align_up(bwd_tc_packed_bytes(), 256);
+    return simt > tc ? simt : tc;
 }
 
 int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl_f32,
@@ -112,8 +114,8 @@ int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float
     if (P <= 0) { set_error("P must be positive (got %d)", P); return GGD_E_INVALID; }
     if (!planes_cl_f32 || !xyz || !flat_params || !packed_f32 || !scratch || !dflat) { set_error("ggd_decode_backward: null required pointer"); return GGD_E_INVALID; }
     if (a.L.variant != 0 && (!out_xyz || !out_scale || !out_rotation || !out_opacity || !out_color)) { set_error("ggd_decode_backward: chained variants need the forward results"); return GGD_E_INVALID; }
-    const BwdStage st = bwd_stage(a.L.pos_dim, (size_t)P);
-    if (scratch_bytes < st.bytes) { set_error("ggd_decode_backward: scratch too small (%zu < %zu)", scratch_bytes, st.bytes); return GGD_E_CAPACITY; }
+    const size_t need = ggd_decode_backward_scratch_bytes(cfg, P);
+    if (scratch_bytes < need) { set_error("ggd_decode_backward: scratch too small (%zu < %zu)", scratch_bytes, need); return GGD_E_CAPACITY; }
     if (reinterpret_cast<uintptr_t>(scratch) & 127) { set_error("scratch must be 128-byte aligned"); return GGD_E_INVALID; }
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     a.planes = planes_cl_f32; a.arch = cfg->arch; a.D = cfg->plane_depth; a.H = cfg->plane_h; a.W = cfg->plane_w;
@@ -127,6 +129,18 @@ int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float
     int dev = 0, sms = 0;
     GGD_CUDA_CHECK(cudaGetDevice(&dev));
     GGD_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (cfg->precision == 1 && cfg->pos_freqs == 0) {
+        // tensor-core chain: stage | forward fp16 pack | transposed fp16 pack, all inside the scratch buffer
+        DecodeBwdTcArgs t;
+        t.b = a;
+        uint8_t* pf = a.stage + align_up(bwd_stage_tc((size_t)P).bytes, 256);
+        uint8_t* pb = pf + align_up(tc_packed_bytes(a.L), 256);
+        if (int e = launch_pack_weights_tc(s, a.L, flat_params, pf)) return e;
+        if (int e = launch_pack_weights_bwd_tc(s, a.L, flat_params, pb)) return e;
+        t.packed_fwd = pf; t.packed_bwd = pb;
+        if (int e = launch_decode_bwd_chain_tc(s, t, sms)) return e;
+        return launch_decode_bwd_dw_mn(s, a.L, a.stage, (size_t)P, dflat, sms);
+    }
     if (int e = launch_decode_bwd_chain(s, a, sms)) return e;
     return launch_decode_bwd_dw(s, a.L, a.stage, (size_t)P, dflat, sms);
 }

@@ -60,6 +60,38 @@ struct DecodeBwdArgs {
     float* dplanes;         // optional: dL/d feature_planes in the generator's NCHW layout [3][32*D][H][W]
 };
 
+// tensor-core chain (decode_bwd_tc.cu): 128-point tiles, [point][feature] operands
+struct BwdStageTc {
+    size_t tiles, x0_tile, h_tile, dz_tile;
+    size_t x0_off, h_off[kHeads][2], dz_off[kHeads][3];   // H_1, H_2 and dZ_0..2 per head; X_0 once
+    size_t bytes;
+};
+__host__ __device__ inline BwdStageTc bwd_stage_tc(size_t P)
+{
+    BwdStageTc s;
+    s.tiles = (P + 127) / 128;
+    s.x0_tile = 128 * 48 * 2;
+    s.h_tile = 128 * 144 * 2;
+    s.dz_tile = 128 * 128 * 2;
+    size_t o = 0;
+    s.x0_off = o; o += s.x0_tile * s.tiles;
+    for (int h = 0; h < kHeads; ++h) {
+        for (int l = 0; l < 2; ++l) { s.h_off[h][l] = o; o += s.h_tile * s.tiles; }
+        for (int l = 0; l < 3; ++l) { s.dz_off[h][l] = o; o += s.dz_tile * s.tiles; }
+    }
+    s.bytes = o;
+    return s;
+}
+size_t bwd_tc_packed_bytes();
+int launch_pack_weights_bwd_tc(cudaStream_t s, const DecoderLayout& L, const float* flat, void* packed);
+struct DecodeBwdTcArgs {
+    DecodeBwdArgs b;              // planes (fp32 channels-last), xyz, outs, douts, stage, dflat, dplanes
+    const uint8_t* packed_fwd;    // decode_tc.cu forward pack (fp16, bias columns folded in)
+    const uint8_t* packed_bwd;    // transposed fp16 pack (launch_pack_weights_bwd_tc)
+};
+int launch_decode_bwd_chain_tc(cudaStream_t s, const DecodeBwdTcArgs& a, int num_sms);
+int launch_decode_bwd_dw_mn(cudaStream_t s, const DecoderLayout& L, const uint8_t* stage, size_t P, float* dflat, int num_sms);
+
 int launch_decode_bwd_chain(cudaStream_t s, const DecodeBwdArgs& a, int num_sms);
 int launch_decode_bwd_dw(cudaStream_t s, const DecoderLayout& L, const uint8_t* stage, size_t P, float* dflat, int num_sms);
 

@@ -1,0 +1,262 @@
+// Body of the tcgen05 decoder backward chain kernel (included by decode_bwd_tc.cu).
+namespace ggd {
+namespace {
+
+// shared memory map (bytes)
+constexpr uint32_t kOffX0 = 256, kOffA = kOffX0 + 128 * kK0 * 2, kOffG = kOffA + 128 * kKH * 2,
+                   kOffDY = kOffG + 3 * kWT12, kOffDy32 = kOffDY + kWT3, kOffW = kOffDy32 + 128 * 4 * 4,
+                   kSmemTotal = kOffW + 2 * kSlotBytes;
+enum { BW_FULL = 0, BW_EMPTY = 2, B_ACC = 4, B_READY = 5 };
+constexpr uint32_t kColAcc = 0, kColY = 128, kColDX = 160;     // TMEM columns
+
+struct StepDesc { uint32_t src_off, bytes; };
+__device__ __forceinline__ StepDesc step_weights(int s)
+{
+    switch (s) {
+        case 0: return {0u, kF0};
+        case 1: return {kF0, kF12};
+        case 2: return {kF0 + kF12, kF12};
+        case 3: return {kF0 + 2 * kF12, kF3};
+        case 4: return {0u, kWT3};
+        case 5: return {kWT3, kWT12};
+        case 6: return {kWT3 + kWT12, kWT12};
+        default: return {kWT3 + 2 * kWT12, kWT0};
+    }
+}
+
+__global__ void __launch_bounds__(kThreadsTc, 1)
+decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const DecodeBwdArgs& a = args.b;
+    const DecoderLayout& L = a.L;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 128);
+    uint8_t* X0 = smem + kOffX0;
+    uint8_t* Abuf = smem + kOffA;
+    float* dy32 = reinterpret_cast<float*>(smem + kOffDy32);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const BwdStageTc st = bwd_stage_tc((size_t)a.P);
+    const int tiles = (int)st.tiles;
+    const int chain0 = kFeat + L.pos_dim;
+
+    if (tid == 0) {
+        for (int i = 0; i < 5; ++i) ptx::mbar_init(&bars[i], 1);
+        ptx::mbar_init(&bars[B_READY], 16);
+        ptx::mbar_fence_init();
+    }
+    if (warp == 16) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 16) {
+        // =============================== epilogue warps ===============================
+        const int r = tid & 127, colq = tid >> 7;
+        const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        if (colq == 0) {   // constant-one column block of the hidden operand
+            *reinterpret_cast<uint4*>(Abuf + canon(r, kHidden, kKH)) = make_uint4(0x00003c00u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(Abuf + canon(r, kHidden + 8, kKH)) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        const size_t plane_stride = (size_t)a.D * a.H * a.W * kFeat;
+        uint32_t n_acc = 0;
+        auto wait_acc = [&]() {
+            if (lane == 0) ptx::mbar_wait(&bars[B_ACC], n_acc & 1);
+            __syncwarp();
+            ++n_acc;
+            ptx::tc_fence_after();
+        };
+        auto signal_ready = [&]() {
+            ptx::tc_fence_before();
+            ptx::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&bars[B_READY]);
+        };
+        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+            const int p0 = tile * kM;
+            // ---- sampling (fp32 planes, 8 lanes per point) into the layer-0 operand ----
+            {
+                const int sub = tid & 7;
+                for (int it = 0; it < 2; ++it) {
+                    const int pt = it * 64 + (tid >> 3), gp = p0 + pt;
+                    float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (gp < a.P) {
+                        const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp);
+                        const float y = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 1);
+                        const float z = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 2);
+                        float4 s0, s1, s2;
+                        if (a.arch == 0) {
+                            s0 = sample4(a.planes, 0, 1, a.H, a.W, x, y, 0.f, sub);
+                            s1 = sample4(a.planes + plane_stride, 0, 1, a.H, a.W, x, z, 0.f, sub);
+                            s2 = sample4(a.planes + 2 * plane_stride, 0, 1, a.H, a.W, z, x, 0.f, sub);
+                        } else {
+                            s0 = sample4(a.planes, 1, a.D, a.H, a.W, x, y, z, sub);
+                            s1 = sample4(a.planes + plane_stride, 1, a.D, a.H, a.W, x, z, y, sub);
+                            s2 = sample4(a.planes + 2 * plane_stride, 1, a.D, a.H, a.W, y, z, x, sub);
+                        }
+                        m = make_float4((s0.x + s1.x + s2.x) / 3.f, (s0.y + s1.y + s2.y) / 3.f,
+                                        (s0.z + s1.z + s2.z) / 3.f, (s0.w + s1.w + s2.w) / 3.f);
+                    }
+                    const __half2 lo = __floats2half2_rn(m.x, m.y), hi = __floats2half2_rn(m.z, m.w);
+                    *reinterpret_cast<uint2*>(X0 + canon(pt, 4 * sub, kK0)) =
+                        make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+                }
+                if (colq == 0) {   // position, chained inputs (saved forward results), zero padding, constant one
+                    const int gp = p0 + r;
+                    auto put = [&](int k, float v) { *reinterpret_cast<__half*>(X0 + canon(r, k, kK0)) = __float2half_rn(v); };
+                    for (int k = kFeat; k < kK0 - 1; ++k) put(k, 0.f);
+                    if (gp < a.P) {
+                        for (int j = 0; j < 3; ++j) put(kFeat + j, __ldg(a.xyz + 3 * (size_t)gp + j));
+                        if (L.variant != 0) {
+                            int col = chain0;
+                            for (int hi = 0; hi < kHeads - 1; ++hi) {
+                                const int h = L.order[hi], n = head_out(h);
+                                for (int j = 0; j < n; ++j) put(col + j, __ldg(a.out[h] + (size_t)gp * n + j));
+                                col += n;
+                            }
+                        }
+                    }
+                    put(kK0 - 1, 1.0f);
+                }
+            }
+            signal_ready();
+
+            for (int hi = kHeads - 1; hi >= 0; --hi) {
+                const int h = L.order[hi], n_out = head_out(h);
+                int my_chain = chain0;
+                for (int e = 0; e < hi; ++e) my_chain += head_out(L.order[e]);
+                const int gp = p0 + r;
+                // ---- forward recompute: layers 0..2 ----
+                for (int l = 0; l < 3; ++l) {
+                    uint8_t* G = smem + kOffG + l * kWT12;
+                    wait_acc();
+                    uint32_t v[32];
+                    ptx::tmem_ld32(trow + kColAcc + colq * 32, v);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        uint32_t og[4], od[4];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            __half2 g, dg;
+                            gelu_and_grad_h2(__floats2half2_rn(__uint_as_float(v[8 * j + 2 * q]), __uint_as_float(v[8 * j + 2 * q + 1])), g, dg);
+                            og[q] = *reinterpret_cast<const uint32_t*>(&g);
+                            od[q] = *reinterpret_cast<const uint32_t*>(&dg);
+                        }
+                        *reinterpret_cast<uint4*>(Abuf + canon(r, colq * 32 + 8 * j, kKH)) = make_uint4(og[0], og[1], og[2], og[3]);
+                        *reinterpret_cast<uint4*>(G + canon(r, colq * 32 + 8 * j, kHidden)) = make_uint4(od[0], od[1], od[2], od[3]);
+                    }
+                    signal_ready();
+                }
+                // ---- last layer: y -> dL/dy (activation derivative, chained gradient from later heads) ----
+                wait_acc();
+                if (colq == 0) {
+                    uint32_t yv[4];
+                    ptx::tmem_ld4(trow + kColY, yv);
+                    ptx::tmem_ld_wait();
+                    float dy[4] = {0.f, 0.f, 0.f, 0.f};
+                    for (int j = 0; j < n_out; ++j) {
+                        float gsum = 0.f;
+                        if (L.variant != 0 && hi < kHeads - 1) gsum = tmem_ld1(trow + kColDX + my_chain + j);
+                        if (gp < a.P) {
+                            if (a.dout[h]) gsum += __ldg(a.dout[h] + (size_t)gp * n_out + j);
+                            float d = 1.f;
+                            if (h == kXyz) d = 0.01f;
+                            if (h == kScale) d = -1.0f / (1.0f + expf(-(__uint_as_float(yv[j]) + 5.0f)));
+                            dy[j] = gsum * d;
+                        }
+                    }
+                    const __half2 d01 = __floats2half2_rn(dy[0], dy[1]), d23 = __floats2half2_rn(dy[2], dy[3]);
+                    uint8_t* DY = smem + kOffDY;
+                    *reinterpret_cast<uint4*>(DY + canon(r, 0, 16)) =
+                        make_uint4(*reinterpret_cast<const uint32_t*>(&d01), *reinterpret_cast<const uint32_t*>(&d23), 0u, 0u);
+                    *reinterpret_cast<uint4*>(DY + canon(r, 8, 16)) = make_uint4(0u, 0u, 0u, 0u);
+                    *reinterpret_cast<float4*>(dy32 + 4 * r) = make_float4(dy[0], dy[1], dy[2], dy[3]);
+                }
+                epi_barrier();
+                // last-layer weight / bias gradient, reduced over the tile: thread = (k = r, j = colq)
+                if (colq < n_out) {
+                    float sacc = 0.f;
+                    for (int p = 0; p < kM; ++p)
+                        sacc = fmaf(dy32[4 * p + colq], __half2float(*reinterpret_cast<const __half*>(Abuf + canon(p, r, kKH))), sacc);
+                    atomicAdd(a.dflat + L.flat_w[h][3] + (size_t)colq * kHidden + r, sacc);
+                    if (r == 0) {
+                        float sb = 0.f;
+                        for (int p = 0; p < kM; ++p) sb += dy32[4 * p + colq];
+                        atomicAdd(a.dflat + L.flat_b[h][3] + colq, sb);
+                    }
+                }
+                signal_ready();
+                // ---- backward: dZ_l = (dZ_{l+1} W_{l+1}) * G_l for l = 2, 1, 0 (in place over G_l) ----
+                for (int l = 2; l >= 0; --l) {
+                    uint8_t* G = smem + kOffG + l * kWT12;
+                    wait_acc();
+                    uint32_t v[32];
+                    ptx::tmem_ld32(trow + kColAcc + colq * 32, v);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        uint4* gp4 = reinterpret_cast<uint4*>(G + canon(r, colq * 32 + 8 * j, kHidden));
+                        uint4 gv = *gp4;
+                        uint32_t* gw = reinterpret_cast<uint32_t*>(&gv);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const __half2 dh = __floats2half2_rn(__uint_as_float(v[8 * j + 2 * q]), __uint_as_float(v[8 * j + 2 * q + 1]));
+                            const __half2 dz = __hmul2(dh, *reinterpret_cast<const __half2*>(&gw[q]));
+                            gw[q] = *reinterpret_cast<const uint32_t*>(&dz);
+                        }
+                        *gp4 = gv;
+                    }
+                    signal_ready();
+                }
+                // ---- dX_0 accumulates in TMEM across heads; nothing to convert ----
+                wait_acc();
+                if (hi > 0) signal_ready();
+            }
+            // ---- feature gradient -> plane gradient (scatter-add), thread = point ----
+            if (a.dplanes && colq == 0) {
+                uint32_t v[32];
+                ptx::tmem_ld32(trow + kColDX, v);
+                ptx::tmem_ld_wait();
+                const int gp = p0 + r;
+                if (gp < a.P) {
+                    const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp);
+                    const float y = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 1);
+                    const float z = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gp + 2);
+                    const size_t gplane = (size_t)kFeat * a.D * a.H * a.W;
+                    for (int c4 = 0; c4 < 8; ++c4) {
+                        const float4 g = make_float4(__uint_as_float(v[4 * c4]) / 3.f, __uint_as_float(v[4 * c4 + 1]) / 3.f,
+                                                     __uint_as_float(v[4 * c4 + 2]) / 3.f, __uint_as_float(v[4 * c4 + 3]) / 3.f);
+                        if (a.arch == 0) {
+                            scatter4(a.dplanes, 0, 1, a.H, a.W, x, y, 0.f, c4, g);
+                            scatter4(a.dplanes + gplane, 0, 1, a.H, a.W, x, z, 0.f, c4, g);
+                            scatter4(a.dplanes + 2 * gplane, 0, 1, a.H, a.W, z, x, 0.f, c4, g);
+                        } else {
+                            scatter4(a.dplanes, 1, a.D, a.H, a.W, x, y, z, c4, g);
+                            scatter4(a.dplanes + gplane, 1, a.D, a.H, a.W, x, z, y, c4, g);
+                            scatter4(a.dplanes + 2 * gplane, 1, a.D, a.H, a.W, y, z, x, c4, g);
+                        }
+                    }
+                }
+            }
+        }
+    }
+#include "decode_bwd_tc_roles.inl"
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 16) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+}  // namespace
+
+int launch_decode_bwd_chain_tc(cudaStream_t s, const DecodeBwdTcArgs& a, int num_sms)
+{
+    GGD_CUDA_CHECK(cudaFuncSetAttribute(decode_bwd_chain_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemTotal));
+    const int tiles = (a.b.P + kM - 1) / kM;
+    decode_bwd_chain_tc_kernel<<<tiles < num_sms ? tiles : num_sms, kThreadsTc, kSmemTotal, s>>>(a);
+    GGD_LAUNCH_CHECK("decode_bwd_chain_tc_kernel");
+    return GGD_OK;
+}
+
+}  // namespace ggd

@@ -95,3 +95,44 @@ __device__ __forceinline__ void sample8h(const __half* __restrict__ plane, int D
 }
 
 }  // namespace ggd
+
+namespace ggd {
+
+// scatter-add of one sample's feature gradient into the generator-layout plane gradient
+__device__ __forceinline__ void scatter4(float* __restrict__ dplane /*[32*D][H][W] of one plane*/, int arch, int D, int H, int W,
+                                         float gx, float gy, float gz, int c4, float4 g)
+{
+    const float ix = ((gx + 1.f) * W - 1.f) * 0.5f, iy = ((gy + 1.f) * H - 1.f) * 0.5f;
+    const float fx0 = floorf(ix), fy0 = floorf(iy);
+    const int x0 = (int)fx0, y0 = (int)fy0;
+    const float wx1 = ix - fx0, wy1 = iy - fy0, wx0 = 1.f - wx1, wy0 = 1.f - wy1;
+    int z0 = 0;
+    float wz0 = 1.f, wz1 = 0.f;
+    if (arch == 1) {
+        const float iz = ((gz + 1.f) * D - 1.f) * 0.5f, fz0 = floorf(iz);
+        z0 = (int)fz0; wz1 = iz - fz0; wz0 = 1.f - wz1;
+    }
+    const size_t HW = (size_t)H * W;
+    const int nz = arch == 1 ? 2 : 1;
+    for (int dz = 0; dz < nz; ++dz) {
+        const int z = z0 + dz;
+        if (z < 0 || z >= D) continue;
+        for (int dy = 0; dy < 2; ++dy) {
+            const int y = y0 + dy;
+            if (y < 0 || y >= H) continue;
+            for (int dx = 0; dx < 2; ++dx) {
+                const int x = x0 + dx;
+                if (x < 0 || x >= W) continue;
+                const float w = (dx ? wx1 : wx0) * (dy ? wy1 : wy0) * (dz ? wz1 : wz0);
+                // generator layout: channel index = c * D + z  (PanoHead/.../renderer.py:51-52)
+                float* p = dplane + ((size_t)(4 * c4) * D + z) * HW + (size_t)y * W + x;
+                atomicAdd(p, w * g.x);
+                atomicAdd(p + (size_t)D * HW, w * g.y);
+                atomicAdd(p + 2 * (size_t)D * HW, w * g.z);
+                atomicAdd(p + 3 * (size_t)D * HW, w * g.w);
+            }
+        }
+    }
+}
+
+}  // namespace ggd

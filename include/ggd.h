@@ -277,7 +277,10 @@ GGD_API int ggd_mlp_forward(void* stream, const float* tri_features, const float
  *   dL_d*         : gradients of the five results; any may be NULL (= zero)
  *   scratch       : ggd_decode_backward_scratch_bytes(cfg, P) bytes of staging
  *   dflat         : [flat_floats] overwritten;  dplanes: overwritten if non-NULL
- * The backward recomputes the forward in fp32 whatever precision the forward ran in. */
+ * cfg->precision selects the flavour: 0 = exact fp32 CUDA-core chain; 1 = tcgen05 chain
+ * (fp16 operands, fp32 accumulation; decoders without the positional embedding — with it
+ * the fp32 chain is used).  Either way the forward is recomputed inside, the planes are the
+ * fp32 channels-last ones and the weight gradients are accumulated on tensor cores. */
 GGD_API size_t ggd_decode_backward_scratch_bytes(const ggd_decoder_config* cfg, int P);
 GGD_API int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl_f32,
                                 const float* xyz, int P, const float* flat_params, const float* packed_f32,
