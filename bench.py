@@ -139,6 +139,9 @@ def run_ours(args, rank, world, dev):
     ms_total = e0.elapsed_time(e1)
     R, over = pipe.check()
     assert not over, "binning capacity overflow inside the timed region"
+    info = (C.c_uint32 * 2)()
+    _lib.check(lib.ggd_raster_binning_info(None, _lib.ptr(pipe.geom), P_FULL, info))
+    binning = {"mode": pipe.bin_mode, "per_tile": bool(info[0]), "longest_tile_list": int(info[1])}
 
     # ---- per-stage times (separate pass, stage events on) ----
     lib.ggd_stage_timing(1)
@@ -222,10 +225,13 @@ def run_ours(args, rank, world, dev):
         "config": {"workload": "configs[1]: PanoHead-arch (tri-grid D=3, 256^2x32ch) SequentialDecoderReverse + "
                                "rasterise, 500k Gaussians, one 512x512 view, random-init decoder weights",
                    "gaussians": P_FULL, "image": SIZE, "num_rendered": R, "fov_deg": FOV,
-                   "l2_policy": "3 rotating input sets (3 x 81.5 MB > 126 MB L2)", "parallelism": f"replicas x{world}"},
+                   "l2_policy": "3 rotating input sets (3 x 81.5 MB > 126 MB L2)", "parallelism": f"replicas x{world}",
+                   "binning": binning},
         "e2e": {"value": round(world * args.steps / e2e_s, 2), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 3 * SIZE * SIZE * 4, "ms_per_step": round(1e3 * e2e_s / args.steps, 3)},
-        "gpu_launches": args.steps * 13,
+        # planes repack, decode, preprocess, scan, blend + binning: tile scan / scatter / tile sort (mode 2), plus
+        # duplicate, 6 digit passes and the range kernel when the radix kernels are enqueued as well (modes 0, 1)
+        "gpu_launches": args.steps * {0: 13, 1: 16, 2: 8}[pipe.bin_mode],
         "clocks": clk.summary(),
         "roofline": {"kernel": "decode_tc_kernel", "bound": "tensor", "achieved": round(flops / (dec_ms * 1e-3) / 1e12, 2),
                      "peak": pk["tf"], "unit": "TFLOP/s", "frac": round(flops / (dec_ms * 1e-3) / 1e12 / pk["tf"], 4),

@@ -51,6 +51,8 @@ SIGNATURES = {
     "ggd_raster_backward": (_i, [_p, _i, _i, _i, _p, _i, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                                  _p, _p, _u64, _p] + [_p] * 10),
     "ggd_raster_status": (_i, [_p, _p, _i, C.POINTER(C.c_uint32)]),
+    "ggd_raster_binning": (_i, [_i]),
+    "ggd_raster_binning_info": (_i, [_p, _p, _i, C.POINTER(C.c_uint32)]),
     "ggd_mark_visible": (_i, [_p, _i, _p, _p, _p, _p]),
     "ggd_raster_field": (_i, [_i, C.c_char_p, _i, _i, _i, _u64, C.POINTER(_sz), C.POINTER(_sz)]),
     "ggd_stage_timing": (_i, [_i]),

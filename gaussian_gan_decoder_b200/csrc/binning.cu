@@ -36,8 +36,9 @@ duplicate_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ means
                  const float* __restrict__ depths, const uint32_t* __restrict__ offsets,
                  const int* __restrict__ radii, uint64_t* __restrict__ keys,
                  uint32_t* __restrict__ vals, uint32_t capacity, uint32_t* __restrict__ counters,
-                 uint32_t* __restrict__ hist, int num_passes)
+                 uint32_t* __restrict__ hist, int num_passes, const uint32_t* __restrict__ skip)
 {
+    if (skip && __ldg(skip)) return;   // frame binned per tile (tile_binning.cu)
     __shared__ uint32_t s_end[kDupThreads];
     __shared__ uint32_t s_depth[kDupThreads];
     __shared__ uint32_t s_rect[kDupThreads];  // x0 | y0 << 16 (tile coordinates, each < 65536)
@@ -400,23 +401,24 @@ int sort_pairs(cudaStream_t s, const uint64_t* keys_in, uint64_t* keys_out, cons
 
 int launch_duplicate(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g,
                      const int* radii, const BinState& b, uint64_t capacity,
-                     const SortScratch& sc, int num_passes)
+                     const SortScratch& sc, int num_passes, const uint32_t* skip)
 {
     const int blocks = (P + kDupThreads - 1) / kDupThreads;
     duplicate_kernel<<<blocks, kDupThreads, 0, s>>>(P, grid_x, grid_y, g.means2D, g.depths,
                                                     g.point_offsets, radii, b.keys_unsorted,
                                                     b.vals_unsorted, (uint32_t)capacity, g.counters,
-                                                    sc.hist, num_passes);
+                                                    sc.hist, num_passes, skip);
     GGD_LAUNCH_CHECK("duplicate_kernel");
     return GGD_OK;
 }
 
 int launch_tile_ranges(cudaStream_t s, const GeomState& g, const BinState& b, uint64_t capacity,
-                       const ImgState& im, int tiles)
+                       const ImgState& im, int tiles, const uint32_t* skip)
 {
     (void)tiles;
     const int blocks = (int)std::max<uint64_t>(1, std::min<uint64_t>((capacity + 255) / 256, 148 * 8));
-    tile_ranges_kernel<<<blocks, 256, 0, s>>>(g.counters + 3, b.keys, im.ranges);
+    // with `skip` the element count comes from counters[6], which is 0 for a frame binned per tile
+    tile_ranges_kernel<<<blocks, 256, 0, s>>>(skip ? g.counters + 6 : g.counters + 3, b.keys, im.ranges);
     GGD_LAUNCH_CHECK("tile_ranges_kernel");
     return GGD_OK;
 }

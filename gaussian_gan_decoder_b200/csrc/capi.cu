@@ -43,7 +43,7 @@ T* take(char*& p, size_t count)
 }
 }  // namespace
 
-GeomState carve_geom(void* base, size_t P)
+GeomState carve_geom(void* base, size_t P, size_t tiles)
 {
     GeomState g;
     char* p = static_cast<char*>(base);
@@ -58,6 +58,7 @@ GeomState carve_geom(void* base, size_t P)
     g.clamped = take<uint8_t>(p, 3 * P);
     g.counters = take<uint32_t>(p, 64);  // counters and scan_status are adjacent: one memset
     g.scan_status = take<uint64_t>(p, (P + kScanTile - 1) / kScanTile + 1);
+    g.tile_counts = take<uint32_t>(p, std::max<size_t>(tiles, 1) * kTileCountStride);   // zeroed by the same memset
     g.bytes = (size_t)(p - static_cast<char*>(base));
     return g;
 }
@@ -109,12 +110,34 @@ int check_common(int P, int W, int H)
     return GGD_OK;
 }
 
+size_t tiles_of(int W, int H) { return (size_t)((W + kTileX - 1) / kTileX) * (size_t)((H + kTileY - 1) / kTileY); }
+
+// How stage 2a bins: 0 = global radix sort only, 1 = per tile when the frame qualifies (decided on the device,
+// both kernel sets enqueued), 2 = per tile only (a frame that does not qualify raises status flag 2).
+// Start-up value from GGD_BINNING ("radix" | "auto" | "tiles"), overridden by ggd_raster_binning().
+int g_binning = -1;
+int binning_mode()
+{
+    if (g_binning < 0) {
+        const char* e = getenv("GGD_BINNING");
+        g_binning = (e && e[0] == 'r') ? 0 : (e && e[0] == 't') ? 2 : 1;
+    }
+    return g_binning;
+}
+
 }  // namespace
 }  // namespace ggd
 
 using namespace ggd;
 
 extern "C" {
+
+int ggd_raster_binning(int mode)
+{
+    const int prev = binning_mode();
+    if (mode >= 0 && mode <= 2) g_binning = mode;
+    return prev;
+}
 
 const char* ggd_last_error(void) { return g_err; }
 int ggd_abi_version(void) { return 1; }
@@ -123,7 +146,7 @@ int ggd_raster_workspace_sizes(int P, int W, int H, uint64_t bin_capacity, size_
 {
     if (P < 0 || W <= 0 || H <= 0 || !sizes_out) { set_error("ggd_raster_workspace_sizes: bad arguments"); return GGD_E_INVALID; }
     if (bin_capacity >= (1ull << 30)) { set_error("bin_capacity %llu exceeds 2^30-1", (unsigned long long)bin_capacity); return GGD_E_INVALID; }
-    sizes_out[0] = carve_geom(nullptr, (size_t)std::max(P, 1)).bytes;
+    sizes_out[0] = carve_geom(nullptr, (size_t)std::max(P, 1), tiles_of(W, H)).bytes;
     sizes_out[1] = carve_bin(nullptr, bin_capacity).bytes;
     sizes_out[2] = carve_img(nullptr, W, H).bytes;
     return GGD_OK;
@@ -147,10 +170,11 @@ int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int H,
     if (rotations && (reinterpret_cast<uintptr_t>(rotations) & 15)) { set_error("rotations must be 16-byte aligned"); return GGD_E_INVALID; }
 
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    GeomState g = carve_geom(geom_ws, (size_t)P);
+    GeomState g = carve_geom(geom_ws, (size_t)P, tiles_of(W, H));
     if (!radii) radii = g.radii;
 
     PreprocessArgs a;
+    a.tile_counts = binning_mode() ? g.tile_counts : nullptr;
     a.P = P; a.D = D; a.M = shs ? M : 0; a.W = W; a.H = H;
     a.means3D = means3D; a.shs = shs; a.colors_precomp = colors_precomp; a.opacities = opacities;
     a.scales = scales; a.scale_modifier = scale_modifier; a.rotations = rotations;
@@ -182,24 +206,36 @@ int ggd_raster_render(void* stream, int P, int W, int H, const float* background
     if (bin_capacity >= (1ull << 30)) { set_error("bin_capacity %llu exceeds 2^30-1", (unsigned long long)bin_capacity); return GGD_E_INVALID; }
 
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    GeomState g = carve_geom(geom_ws, (size_t)P);
+    GeomState g = carve_geom(geom_ws, (size_t)P, tiles_of(W, H));
     BinState b = carve_bin(bin_ws, bin_capacity);
     ImgState im = carve_img(img_ws, W, H);
     if (!radii) radii = g.radii;
     const int grid_x = (W + kTileX - 1) / kTileX, grid_y = (H + kTileY - 1) / kTileY;
     const int tiles = grid_x * grid_y;
+    const bool per_tile = binning_mode() != 0 && bin_capacity > 0;
+    const bool radix = !(per_tile && binning_mode() == 2);   // enqueue the radix kernels
     const int end_bit = 32 + tile_key_bits((uint32_t)tiles);
     const int num_passes = (end_bit + kRadixBits - 1) / kRadixBits;
 
     SortScratch sc = carve_sort_scratch(b.sort_scratch, bin_capacity);
-    GGD_CUDA_CHECK(cudaMemsetAsync(b.sort_scratch, 0, sc.zero_bytes, s));
-    GGD_CUDA_CHECK(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)tiles, s));
-    { StageScope t(s, kStDuplicate); if (int e = launch_duplicate(s, P, grid_x, grid_y, g, radii, b, bin_capacity, sc, num_passes)) return e; }
+    if (radix) GGD_CUDA_CHECK(cudaMemsetAsync(b.sort_scratch, 0, sc.zero_bytes, s));
+    const uint32_t* skip = per_tile ? g.counters + 4 : nullptr;
+    {
+        StageScope t(s, kStDuplicate);
+        if (per_tile) {   // writes every range, picks the path for this frame (counters[4])
+            if (int e = launch_tile_scan(s, g, im, tiles, bin_capacity, P, !radix)) return e;
+            if (int e = launch_tile_scatter(s, P, grid_x, grid_y, g, radii, b, im, bin_capacity)) return e;
+        } else {
+            GGD_CUDA_CHECK(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)tiles, s));
+        }
+        if (radix) if (int e = launch_duplicate(s, P, grid_x, grid_y, g, radii, b, bin_capacity, sc, num_passes, skip)) return e;
+    }
     if (bin_capacity > 0) {
         { StageScope t(s, kStSort);
-          if (int e = sort_pairs(s, b.keys_unsorted, b.keys, b.vals_unsorted, b.vals, g.counters + 3,
-                                 bin_capacity, 0, end_bit, b.keys_tmp, b.vals_tmp, sc, true)) return e; }
-        { StageScope t(s, kStRanges); if (int e = launch_tile_ranges(s, g, b, bin_capacity, im, tiles)) return e; }
+          if (per_tile) if (int e = launch_tile_sort(s, g, b, im, tiles)) return e;
+          if (radix) if (int e = sort_pairs(s, b.keys_unsorted, b.keys, b.vals_unsorted, b.vals, g.counters + (per_tile ? 6 : 3),
+                                            bin_capacity, 0, end_bit, b.keys_tmp, b.vals_tmp, sc, true)) return e; }
+        { StageScope t(s, kStRanges); if (radix) if (int e = launch_tile_ranges(s, g, b, bin_capacity, im, tiles, skip)) return e; }
     }
     const float* features = colors_precomp ? colors_precomp : g.rgb;
     StageScope t(s, kStBlend);
@@ -229,6 +265,16 @@ int ggd_raster_status(void* stream, const void* geom_ws, int P, uint32_t out[2])
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     GeomState g = carve_geom(const_cast<void*>(geom_ws), (size_t)P);
     GGD_CUDA_CHECK(cudaMemcpyAsync(out, g.counters, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    GGD_CUDA_CHECK(cudaStreamSynchronize(s));
+    return GGD_OK;
+}
+
+int ggd_raster_binning_info(void* stream, const void* geom_ws, int P, uint32_t out[2])
+{
+    if (!geom_ws || !out || P <= 0) { set_error("ggd_raster_binning_info: bad arguments"); return GGD_E_INVALID; }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    GeomState g = carve_geom(const_cast<void*>(geom_ws), (size_t)P);
+    GGD_CUDA_CHECK(cudaMemcpyAsync(out, g.counters + 4, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     GGD_CUDA_CHECK(cudaStreamSynchronize(s));
     return GGD_OK;
 }

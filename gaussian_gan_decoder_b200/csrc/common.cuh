@@ -78,8 +78,11 @@ struct GeomState {
     uint32_t* tiles_touched;  // [P]
     uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched
     uint8_t* clamped;         // [P][3]
-    uint32_t* counters;       // [0] num_rendered, [1] overflow flag, [2] scan ticket
+    uint32_t* counters;       // [0] num_rendered, [1] overflow flag, [2] scan ticket, [3] clamped count,
+                              // [4] 1 = this frame is binned per tile (tile_binning.cu), [5] longest tile list
     uint64_t* scan_status;    // [scan tiles] decoupled look-back words of the scan
+    uint32_t* tile_counts;    // [tiles][kTileCountStride] instances per tile, counted by preprocess; one 128-byte line
+                              // per tile so the atomics spread over the L2 slices (last field: size depends on W, H)
     size_t bytes;
 };
 struct BinState {
@@ -99,7 +102,7 @@ struct ImgState {
     uint2* ranges;        // [tiles]
     size_t bytes;
 };
-GeomState carve_geom(void* base, size_t P);
+GeomState carve_geom(void* base, size_t P, size_t tiles = 0);
 BinState carve_bin(void* base, uint64_t capacity);
 ImgState carve_img(void* base, int W, int H);
 
@@ -124,14 +127,23 @@ struct PreprocessArgs {
     float tan_fovx, tan_fovy, focal_x, focal_y;
     int prefiltered;
     int grid_x, grid_y;
+    uint32_t* tile_counts;   // optional [grid_x * grid_y][32]: word 0 += 1 for every tile a splat touches
 };
 int launch_preprocess(cudaStream_t s, const PreprocessArgs& a, const GeomState& g, int* radii);
 int launch_scan(cudaStream_t s, int P, const GeomState& g);
+// `skip` (optional, device): the kernels return at once when *skip != 0 (frame binned per tile instead)
 int launch_duplicate(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g,
                      const int* radii, const BinState& b, uint64_t capacity,
-                     const SortScratch& sc, int num_passes);
+                     const SortScratch& sc, int num_passes, const uint32_t* skip = nullptr);
 int launch_tile_ranges(cudaStream_t s, const GeomState& g, const BinState& b, uint64_t capacity,
-                       const ImgState& im, int tiles);
+                       const ImgState& im, int tiles, const uint32_t* skip = nullptr);
+// per-tile binning (tile_binning.cu)
+constexpr uint32_t kTileCountStride = 32;  // words between two tiles' counters
+constexpr uint32_t kTileSortMax = 4096;   // longest tile list the shared-memory sort takes
+int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int tiles, uint64_t capacity, int P, bool strict);
+int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g, const int* radii,
+                        const BinState& b, const ImgState& im, uint64_t capacity);
+int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, const ImgState& im, int tiles);
 int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const GeomState& g,
                  const BinState& b, const ImgState& im, const float* features,
                  const float* background, float* out_color);

@@ -271,6 +271,9 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
                     conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, __ldg(a.opacities + idx));
                     my_radius_i = (int)my_radius;
                     my_tiles = area;
+                    if (a.tile_counts)   // per-tile list lengths for tile_binning.cu
+                        for (uint32_t ty = rmin.y; ty < rmax.y; ++ty)
+                            for (uint32_t tx = rmin.x; tx < rmax.x; ++tx) atomicAdd(a.tile_counts + (size_t)(ty * a.grid_x + tx) * 32, 1u);
                 }
             }
         }

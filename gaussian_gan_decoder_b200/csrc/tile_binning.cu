@@ -1,0 +1,370 @@
+// Stage 2a, per-tile flavour: bin the instances by tile first, then sort every tile's list by depth
+// inside shared memory.
+//
+// Replaces the same reference code as binning.cu — duplicateWithKeys
+// (DGR/cuda_rasterizer/rasterizer_impl.cu:70-111), cub::DeviceRadixSort::SortPairs (:303-308) and
+// identifyTileRanges (:116-138) — and produces the same bits: the reference sorts the keys
+// (tile << 32 | depth bits) with a STABLE sort whose input order is Gaussian index ascending, so within
+// a tile the order is (depth bits, Gaussian index) ascending, and a Gaussian appears at most once per
+// tile.  Sorting each tile's (depth bits << 32 | Gaussian index) words is therefore the same permutation.
+//
+// Why: the global radix sort moves 6 x 24 bytes per instance through HBM in 6 dependent passes, each a
+// launch with a chained look-back; at the frame sizes of the headline workload (R ~ 10^6 instances,
+// ~800 per tile) that is latency, not bandwidth.  Here an instance is written once into its tile's
+// segment and sorted where it lands:
+//   preprocess        counts instances per tile (atomics, fused into the projection kernel)
+//   tile_scan_kernel  exclusive scan of the counts -> ranges[tile] = [start, end) ((0,0) for an empty
+//                     tile, as the reference leaves it); turns each counter into the tile's write
+//                     cursor; decides whether the frame qualifies (longest list <= kTileSortMax,
+//                     R <= capacity)
+//   tile_scatter      slot-centric like duplicate_kernel; claims a slot in the tile's segment with an
+//                     atomic on the tile's cursor
+//   tile_sort_kernel  one CTA per tile: distribution sort of the 64-bit words in shared memory (bitonic
+//                     network for lists with heavily clustered depths)
+// Frames that do not qualify (a tile list longer than kTileSortMax) take the radix path of binning.cu;
+// the decision is made on the device (counters[4]) and both sets of kernels are always enqueued, the
+// ones that do not apply return at once, so no host round trip is needed.
+#include "common.cuh"
+
+namespace ggd {
+namespace {
+
+constexpr int kScanThreadsT = 1024;
+
+__global__ void __launch_bounds__(kScanThreadsT)
+tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int tiles, uint32_t capacity,
+                 const uint32_t* __restrict__ offsets, int P, uint32_t* __restrict__ counters, int strict)
+{
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_max, s_carry;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    uint32_t mx = 0;
+    for (int i = t; i < tiles; i += kScanThreadsT) mx = max(mx, counts[(size_t)i * kTileCountStride]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) s_warp[warp] = mx;
+    __syncthreads();
+    if (t == 0) {
+        uint32_t m = 0;
+        for (int w = 0; w < kScanThreadsT / 32; ++w) m = max(m, s_warp[w]);
+        const uint32_t R = P > 0 ? __ldg(offsets + P - 1) : 0u;
+        const bool per_tile = m <= kTileSortMax && R <= capacity;
+        s_max = per_tile ? 1u : 0u;
+        s_carry = 0;
+        // flag 1: more instances than the buffers hold; flag 2: the caller enqueued no radix kernels but this
+        // frame needs them.  Either way the image is undefined and the caller runs the stage again.
+        counters[1] = ((R > capacity) ? 1u : 0u) | ((strict && !per_tile) ? 2u : 0u);
+        counters[3] = min(R, capacity);
+        counters[4] = per_tile ? 1u : 0u;
+        counters[5] = m;
+        counters[6] = per_tile ? 0u : min(R, capacity);   // element count the radix kernels see
+    }
+    __syncthreads();
+    const bool per_tile = s_max != 0;
+    if (!per_tile) {   // the radix path's range kernel expects zeros for empty tiles
+        for (int i = t; i < tiles; i += kScanThreadsT) ranges[i] = make_uint2(0u, 0u);
+        return;
+    }
+    for (int base = 0; base < tiles; base += kScanThreadsT) {
+        const int i = base + t;
+        const uint32_t v = i < tiles ? counts[(size_t)i * kTileCountStride] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        __syncthreads();
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t off = s_carry;
+        for (int w = 0; w < warp; ++w) off += s_warp[w];
+        if (i < tiles) {
+            const uint32_t start = off + incl - v;
+            ranges[i] = v ? make_uint2(start, start + v) : make_uint2(0u, 0u);
+            counts[(size_t)i * kTileCountStride] = start;   // from here on: the tile's write cursor
+        }
+        __syncthreads();
+        if (t == kScanThreadsT - 1) s_carry = off + incl;
+        __syncthreads();
+    }
+}
+
+constexpr int kScatterThreads = 256;
+
+// Same slot-centric walk as duplicate_kernel (binning.cu): CTA = 256 Gaussians' slot interval, thread =
+// slots s, s+256, ...; additionally to the reference-order key/value arrays (kept for the debug
+// accessors) every instance claims a place in its tile's segment.
+__global__ void __launch_bounds__(kScatterThreads)
+tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ means2D,
+                    const float* __restrict__ depths, const uint32_t* __restrict__ offsets,
+                    const int* __restrict__ radii, uint64_t* __restrict__ keys_unsorted,
+                    uint32_t* __restrict__ vals_unsorted, uint64_t* __restrict__ words, uint32_t* __restrict__ cursors,
+                    const uint32_t* __restrict__ counters)
+{
+    if (__ldg(counters + 4) == 0u) return;
+    __shared__ uint32_t s_end[kScatterThreads];
+    __shared__ uint32_t s_depth[kScatterThreads];
+    __shared__ uint32_t s_rect[kScatterThreads];
+    __shared__ uint32_t s_w[kScatterThreads];
+    const int t = threadIdx.x;
+    const int base = blockIdx.x * kScatterThreads;
+    const int idx = base + t;
+    const uint32_t block_start = (base == 0) ? 0u : __ldg(offsets + base - 1);
+    uint32_t my_end = 0;
+    if (idx < P) {
+        my_end = __ldg(offsets + idx);
+        const int r = __ldg(radii + idx);
+        uint32_t x0 = 0, y0 = 0, w = 0;
+        if (r > 0) {
+            uint2 rmin, rmax;
+            tile_rect(__ldg(means2D + idx), r, grid_x, grid_y, rmin, rmax);
+            x0 = rmin.x; y0 = rmin.y; w = rmax.x - rmin.x;
+            s_depth[t] = __float_as_uint(__ldg(depths + idx));
+        }
+        s_rect[t] = x0 | (y0 << 16);
+        s_w[t] = w;
+    }
+    s_end[t] = (idx < P) ? my_end : 0xffffffffu;
+    __syncthreads();
+    const int last = min(kScatterThreads, P - base) - 1;
+    const uint32_t block_end = s_end[last];
+    for (uint32_t s = block_start + t; s < block_end; s += kScatterThreads) {
+        int lo = 0, hi = last;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int mid = (lo + hi) >> 1;
+            if (s_end[mid] > s) hi = mid; else lo = mid + 1;
+        }
+        const int g = lo;
+        const uint32_t g_start = (g == 0) ? block_start : s_end[g - 1];
+        const uint32_t j = s - g_start;
+        const uint32_t w = s_w[g];
+        const uint32_t rc = s_rect[g];
+        const uint32_t tile = ((rc >> 16) + j / w) * (uint32_t)grid_x + (rc & 0xffffu) + j % w;
+        const uint32_t depth = s_depth[g], id = (uint32_t)(base + g);
+        keys_unsorted[s] = ((uint64_t)tile << 32) | depth;
+        vals_unsorted[s] = id;
+        const uint32_t pos = atomicAdd(cursors + (size_t)tile * kTileCountStride, 1u);
+        words[pos] = ((uint64_t)depth << 32) | id;
+    }
+}
+
+constexpr int kTileSortThreads = 256;
+
+// Bitonic sort of n_pad = 256 * E words, E consecutive words per thread ("blocked"): compare distances
+// below E stay inside a thread's registers, distances below 32 E are warp shuffles, and only the three
+// largest distances (6 of the network's stages, whatever n_pad is) go through shared memory.
+template <int E>
+__device__ __forceinline__ void sort_tile(uint64_t* __restrict__ s, const uint64_t* __restrict__ words, uint32_t begin,
+                                          uint32_t n, uint32_t tile, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+{
+    constexpr uint32_t n_pad = kTileSortThreads * E;
+    const int t = threadIdx.x;
+    for (uint32_t i = t; i < n_pad; i += kTileSortThreads) s[i] = i < n ? __ldg(words + begin + i) : ~0ull;
+    __syncthreads();
+    uint64_t v[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) v[r] = s[t * E + r];
+    const uint32_t e0 = (uint32_t)t * E;
+#pragma unroll 1
+    for (uint32_t k = 2; k <= n_pad; k <<= 1) {
+#pragma unroll 1
+        for (uint32_t j = k >> 1; j >= (uint32_t)E; j >>= 1) {   // partner word lives in another thread
+            const uint32_t jt = j / E;                            // distance in threads
+            const bool take_min = (((e0 & j) == 0) == ((e0 & k) == 0));
+            if (jt >= 32) {
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < E; ++r) s[t * E + r] = v[r];
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    const uint64_t o = s[(t ^ jt) * E + r];
+                    v[r] = take_min ? min(v[r], o) : max(v[r], o);
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    const uint64_t o = __shfl_xor_sync(0xffffffffu, v[r], jt);
+                    v[r] = take_min ? min(v[r], o) : max(v[r], o);
+                }
+            }
+        }
+        // distances below E: inside the thread.  Direction is per word for k <= E / 2, per thread above.
+#pragma unroll
+        for (int j = E >> 1; j > 0; j >>= 1) {
+            if ((uint32_t)j < k) {
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    if ((r & j) == 0) {
+                        const bool up = ((e0 + r) & k) == 0;
+                        const uint64_t a = v[r], b = v[r | j];
+                        const uint64_t lo = min(a, b), hi = max(a, b);
+                        v[r] = up ? lo : hi;
+                        v[r | j] = up ? hi : lo;
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < E; ++r) s[t * E + r] = v[r];
+    __syncthreads();
+    for (uint32_t i = t; i < n; i += kTileSortThreads) {
+        const uint64_t w = s[i];
+        vals[begin + i] = (uint32_t)w;
+        keys[begin + i] = ((uint64_t)tile << 32) | (w >> 32);
+    }
+}
+
+// Distribution sort of one tile list (n <= 256 E words, thread t holds words t, t + 256, ...): the depth
+// bits of a tile's instances are spread over a narrow interval, so a monotone map of [min, max] onto 256 E
+// buckets leaves about one word per bucket.  Words are dropped into their bucket (shared-memory atomics
+// hand out the rank inside the bucket), bucket starts come from one scan, and the thread owning a bucket
+// orders its few words by insertion.  O(n) instead of the bitonic network's O(n log^2 n); a list with an
+// overfull bucket (many equal or clustered depths) falls back to the network.
+constexpr uint32_t kMaxBucket = 16;
+
+template <int E>
+__device__ __forceinline__ void dist_sort_tile(uint64_t* __restrict__ s_out, uint32_t* __restrict__ s_hist,
+                                               const uint64_t* __restrict__ words, uint32_t begin, uint32_t n, uint32_t tile,
+                                               uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+{
+    constexpr uint32_t n_b = kTileSortThreads * E;
+    __shared__ uint32_t s_red[2][kTileSortThreads / 32];
+    __shared__ uint32_t s_part[kTileSortThreads / 32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    uint64_t w[E];
+    uint32_t dmin = 0xffffffffu, dmax = 0u;
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const uint32_t i = t + r * kTileSortThreads;
+        w[r] = i < n ? __ldg(words + begin + i) : ~0ull;
+        if (i < n) { dmin = min(dmin, (uint32_t)(w[r] >> 32)); dmax = max(dmax, (uint32_t)(w[r] >> 32)); }
+        s_hist[i] = 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        dmin = min(dmin, __shfl_xor_sync(0xffffffffu, dmin, o));
+        dmax = max(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+    }
+    if (lane == 0) { s_red[0][warp] = dmin; s_red[1][warp] = dmax; }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kTileSortThreads / 32; ++k) { dmin = min(dmin, s_red[0][k]); dmax = max(dmax, s_red[1][k]); }
+    const float scale = (float)n_b / ((float)(dmax - dmin) + 1.0f);
+    uint32_t bk[E];   // bucket | rank inside the bucket << 16
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const uint32_t i = t + r * kTileSortThreads;
+        bk[r] = 0;
+        if (i < n) {
+            const uint32_t b = min(n_b - 1u, (uint32_t)((float)((uint32_t)(w[r] >> 32) - dmin) * scale));
+            bk[r] = b | (atomicAdd(&s_hist[b], 1u) << 16);
+        }
+    }
+    __syncthreads();
+    // exclusive scan of the bucket counts; thread t owns buckets [t E, t E + E)
+    uint32_t cnt[E], sum = 0, big = 0;
+#pragma unroll
+    for (int q = 0; q < E; ++q) { cnt[q] = s_hist[t * E + q]; sum += cnt[q]; big = max(big, cnt[q]); }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_part[warp] = incl;
+    const bool overfull = __syncthreads_or(big > kMaxBucket);
+    uint32_t start = incl - sum;
+#pragma unroll
+    for (int k = 0; k < kTileSortThreads / 32; ++k) if (k < warp) start += s_part[k];
+    if (overfull) {   // uniform for the CTA
+        sort_tile<E>(s_out, words, begin, n, tile, keys, vals);
+        return;
+    }
+    {
+        uint32_t run = start;
+#pragma unroll
+        for (int q = 0; q < E; ++q) { s_hist[t * E + q] = run; run += cnt[q]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < E; ++r)
+        if (t + r * kTileSortThreads < n) s_out[s_hist[bk[r] & 0xffffu] + (bk[r] >> 16)] = w[r];
+    __syncthreads();
+    {
+        uint32_t b0 = start;
+#pragma unroll
+        for (int q = 0; q < E; ++q) {
+            const uint32_t m = cnt[q];
+            for (uint32_t i = 1; i < m; ++i) {   // insertion sort of bucket [b0, b0 + m)
+                const uint64_t x = s_out[b0 + i];
+                uint32_t j = i;
+                while (j > 0 && s_out[b0 + j - 1] > x) { s_out[b0 + j] = s_out[b0 + j - 1]; --j; }
+                s_out[b0 + j] = x;
+            }
+            b0 += m;
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = t; i < n; i += kTileSortThreads) {
+        const uint64_t x = s_out[i];
+        vals[begin + i] = (uint32_t)x;
+        keys[begin + i] = ((uint64_t)tile << 32) | (x >> 32);
+    }
+}
+
+__global__ void __launch_bounds__(kTileSortThreads)
+tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ words,
+                 uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters)
+{
+    if (__ldg(counters + 4) == 0u) return;
+    extern __shared__ __align__(16) uint8_t s_dyn[];
+    uint64_t* s = reinterpret_cast<uint64_t*>(s_dyn);                              // [kTileSortMax]
+    uint32_t* h = reinterpret_cast<uint32_t*>(s_dyn + sizeof(uint64_t) * kTileSortMax);   // [kTileSortMax]
+    const uint32_t tile = blockIdx.x;
+    const uint2 range = ranges[tile];
+    const uint32_t n = range.y - range.x;
+    if (n == 0) return;
+    if (n <= 256) dist_sort_tile<1>(s, h, words, range.x, n, tile, keys, vals);
+    else if (n <= 512) dist_sort_tile<2>(s, h, words, range.x, n, tile, keys, vals);
+    else if (n <= 1024) dist_sort_tile<4>(s, h, words, range.x, n, tile, keys, vals);
+    else if (n <= 2048) dist_sort_tile<8>(s, h, words, range.x, n, tile, keys, vals);
+    else dist_sort_tile<16>(s, h, words, range.x, n, tile, keys, vals);
+}
+
+}  // namespace
+
+int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int tiles, uint64_t capacity, int P, bool strict)
+{
+    tile_scan_kernel<<<1, kScanThreadsT, 0, s>>>(g.tile_counts, im.ranges, tiles, (uint32_t)capacity, g.point_offsets, P,
+                                                 g.counters, strict ? 1 : 0);
+    GGD_LAUNCH_CHECK("tile_scan_kernel");
+    return GGD_OK;
+}
+
+int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g, const int* radii,
+                        const BinState& b, const ImgState& im, uint64_t capacity)
+{
+    (void)capacity; (void)im;
+    const int blocks = (P + kScatterThreads - 1) / kScatterThreads;
+    tile_scatter_kernel<<<blocks, kScatterThreads, 0, s>>>(P, grid_x, grid_y, g.means2D, g.depths, g.point_offsets, radii,
+                                                           b.keys_unsorted, b.vals_unsorted, b.keys_tmp, g.tile_counts,
+                                                           g.counters);
+    GGD_LAUNCH_CHECK("tile_scatter_kernel");
+    return GGD_OK;
+}
+
+int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, const ImgState& im, int tiles)
+{
+    constexpr int smem = (int)((sizeof(uint64_t) + sizeof(uint32_t)) * kTileSortMax);
+    GGD_CUDA_CHECK(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    tile_sort_kernel<<<tiles, kTileSortThreads, smem, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters);
+    GGD_LAUNCH_CHECK("tile_sort_kernel");
+    return GGD_OK;
+}
+
+}  // namespace ggd

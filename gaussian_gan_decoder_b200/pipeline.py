@@ -30,6 +30,9 @@ class FramePipeline:
         self.capacity = None
         self.geom = self.binning = self.img = None
         self.pinned = torch.zeros(4, dtype=torch.int32).pin_memory()
+        # stage-2 binning mode of this loop (ggd_raster_binning): starts at the library's setting; check() moves
+        # it to 2 (tiles only: no radix launches) once a frame qualified, and back to 1 if one did not.
+        self.bin_mode = self.lib.ggd_raster_binning(-1)
         self._alloc(capacity or 4 * P)
 
     def _alloc(self, capacity):
@@ -56,15 +59,23 @@ class FramePipeline:
                                           p(self.out["xyz"]), p(self.out["scale"]), p(self.out["rotation"]),
                                           p(self.out["opacity"]), p(self.out["color"]),
                                           p(self.act["scale"]), p(self.act["rotation"]), p(self.act["opacity"])))
-        import math
-        _lib.check(lib.ggd_raster_forward(
-            s, P, 0, 1, p(bg), self.W, self.H, p(self.out["xyz"]), p(self.out["color"]), None,
-            p(self.act["opacity"]), p(self.act["scale"]), 1.0, p(self.act["rotation"]), None,
-            p(cam.world_view_transform), p(cam.full_proj_transform), p(cam.camera_center),
-            math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), 0,
-            p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
-            C.c_void_p(self.pinned.data_ptr())))
+        self._raster(s, cam, bg)
         return self.image
+
+    def _raster(self, s, cam, bg):
+        import math
+        lib, p, P = self.lib, _lib.ptr, self.P
+        prev = lib.ggd_raster_binning(self.bin_mode)
+        try:
+            _lib.check(lib.ggd_raster_forward(
+                s, P, 0, 1, p(bg), self.W, self.H, p(self.out["xyz"]), p(self.out["color"]), None,
+                p(self.act["opacity"]), p(self.act["scale"]), 1.0, p(self.act["rotation"]), None,
+                p(cam.world_view_transform), p(cam.full_proj_transform), p(cam.camera_center),
+                math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), 0,
+                p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
+                C.c_void_p(self.pinned.data_ptr())))
+        finally:
+            lib.ggd_raster_binning(prev)
 
     def capture(self, planes_nchw, xyz, cam, bg):
         """Record one frame (planes -> decode -> rasterise) into a CUDA graph.  The graph reads the given
@@ -82,24 +93,25 @@ class FramePipeline:
     def render_only(self, cam, bg):
         """Another view of the attributes decoded by the last ``frame()`` (decoded attributes depend
         on the latent only): rasterise again with a different camera."""
-        import math
-        lib, p, P = self.lib, _lib.ptr, self.P
-        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        _lib.check(lib.ggd_raster_forward(
-            s, P, 0, 1, p(bg), self.W, self.H, p(self.out["xyz"]), p(self.out["color"]), None,
-            p(self.act["opacity"]), p(self.act["scale"]), 1.0, p(self.act["rotation"]), None,
-            p(cam.world_view_transform), p(cam.full_proj_transform), p(cam.camera_center),
-            math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), 0,
-            p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
-            C.c_void_p(self.pinned.data_ptr())))
+        self._raster(C.c_void_p(torch.cuda.current_stream().cuda_stream), cam, bg)
         return self.image
 
     def check(self):
-        """Synchronise and verify the last frame fit the binning buffer; grows it otherwise.
-        Returns (num_rendered, overflowed)."""
+        """Synchronise and verify the last frame: it must fit the binning buffer (grown otherwise) and, in
+        binning mode 2, must have qualified for per-tile binning (mode falls back to 1 otherwise).
+        Returns (num_rendered, redo): ``redo`` means the last image is invalid, enqueue the frame again."""
         torch.cuda.current_stream().synchronize()
         R = int(self.pinned[0].item()) & 0xffffffff
         over = R > self.capacity
         if over:
             self._alloc(int(R * 1.25) + 4096)
+        if self.bin_mode:
+            st, info = (C.c_uint32 * 2)(), (C.c_uint32 * 2)()
+            s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _lib.check(self.lib.ggd_raster_status(s, _lib.ptr(self.geom), self.P, st))
+            _lib.check(self.lib.ggd_raster_binning_info(s, _lib.ptr(self.geom), self.P, info))
+            if st[1] & 2:
+                self.bin_mode, over = 1, True
+            elif self.bin_mode == 1 and info[0] and not over:
+                self.bin_mode = 2
         return R, over

@@ -126,6 +126,22 @@ GGD_API int ggd_raster_backward(void* stream, int P, int D, int M, const float* 
  * (rasterizer_impl.cu:336); here it is a separate, optional query. */
 GGD_API int ggd_raster_status(void* stream, const void* geom_ws, int P, uint32_t out[2]);
 
+/* How stage 2 orders the instances.  mode 1 (default; env GGD_BINNING=auto): frames whose longest tile
+ * list is at most 4096 are binned per tile and each list is sorted in shared memory
+ * (csrc/tile_binning.cu); other frames take the global radix sort.  mode 0 (GGD_BINNING=radix): always
+ * the radix sort.  Both produce the bits of the reference's duplicateWithKeys + stable SortPairs +
+ * identifyTileRanges (rasterizer_impl.cu:70-138, :303-318).  The per-frame choice is made on the
+ * device.  mode 2 (GGD_BINNING=tiles): like 1 but the radix kernels are not even enqueued (saves their
+ * launches); a frame that turns out to need them raises flag 2 in ggd_raster_status's second word, its
+ * image is undefined and the caller runs it again in mode 1 -- for frame loops whose scenes are known
+ * to qualify.  Pass -1 to query.  Returns the previous mode.  Process-wide; the state buffers of a
+ * frame must be rendered with the mode its preprocess call ran under.  No reference counterpart. */
+GGD_API int ggd_raster_binning(int mode);
+
+/* Blocking read-back of { binned_per_tile, longest_tile_list } of the last frame in geom_ws
+ * (longest_tile_list is only counted in modes 1 and 2).  No reference counterpart. */
+GGD_API int ggd_raster_binning_info(void* stream, const void* geom_ws, int P, uint32_t out[2]);
+
 /* Frustum test only.  Replaces Rasterizer::markVisible → checkFrustum
  * (rasterizer_impl.cu:54-66, :141-152).  `present` is P bytes (bool). */
 GGD_API int ggd_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix,

@@ -264,3 +264,58 @@ def test_mark_visible(cuda):
     z = pts @ view[:3, 2] + view[3, 2]
     expect = z > 0.2
     assert vis.dtype == torch.bool and int((vis != expect).sum()) <= 2
+
+
+@pytest.mark.parametrize("P,size,trained,expect_per_tile", [
+    (257, 100, True, True), (50000, 512, False, True), (500_000, 512, False, True),
+    (400_000, 64, True, False),      # 16 tiles only: lists far longer than the shared-memory sort takes
+])
+def test_binning_modes_agree(cuda, P, size, trained, expect_per_tile):
+    """Per-tile binning (tile_binning.cu) and the global radix sort give the same bits; the per-frame choice
+    is made on the device from the longest tile list."""
+    lib = _lib.load()
+    s = synthetic.raster_scene(P, size=size, seed_offset=11)
+    if not trained:
+        s = random_init_like(s, 5)
+    s = to_dev(s, cuda)
+    prev = lib.ggd_raster_binning(1)
+    try:
+        auto = run_ours(s, cuda)
+        info = (C.c_uint32 * 2)()
+        _lib.check(lib.ggd_raster_binning_info(None, C.c_void_p(auto["_buffers"][0].data_ptr()), P, info))
+        assert bool(info[0]) == expect_per_tile, (info[0], info[1])
+        assert (info[1] <= 4096) == expect_per_tile
+        lib.ggd_raster_binning(0)
+        radix = run_ours(s, cuda)
+    finally:
+        lib.ggd_raster_binning(prev)
+    assert_bit_exact(auto, radix, P)
+    counts = (auto["ranges"].view(-1, 2)[:, 1] - auto["ranges"].view(-1, 2)[:, 0])
+    assert int(counts.max()) == info[1]
+    assert int(counts.sum()) == auto["R"]
+
+
+def test_binning_clustered_depths(cuda):
+    """All splats at (nearly) one depth: every tile list collapses into a few buckets of the distribution
+    sort, which must hand over to its comparison network; ties in depth are ordered by Gaussian index."""
+    lib = _lib.load()
+    P = 60_000
+    s = synthetic.raster_scene(P, size=256, seed_offset=3)
+    V = s["viewmatrix"]
+    d = V[:3, 2] / V[:3, 2].norm()
+    s["means3D"] = (s["means3D"] - (s["means3D"] @ d)[:, None] * d[None, :]).contiguous()
+    s = to_dev(s, cuda)
+    prev = lib.ggd_raster_binning(1)
+    try:
+        auto = run_ours(s, cuda)
+        info = (C.c_uint32 * 2)()
+        _lib.check(lib.ggd_raster_binning_info(None, C.c_void_p(auto["_buffers"][0].data_ptr()), P, info))
+        assert info[0] == 1 and info[1] > 64
+        lib.ggd_raster_binning(0)
+        radix = run_ours(s, cuda)
+    finally:
+        lib.ggd_raster_binning(prev)
+    assert auto["R"] > 0
+    depth_bits = auto["point_list_keys"] & 0xffffffff
+    assert depth_bits.unique().numel() < 64            # the scene really is degenerate in depth
+    assert_bit_exact(auto, radix, P)
