@@ -85,10 +85,10 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                 const int sub = e & 3, pt = e >> 2, gps = p0 + pt;
                 const __half* pl = reinterpret_cast<const __half*>(a.planes);
                 float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                float rx = 0.f, ry = 0.f, rz = 0.f;
                 if (gps < a.P) {
-                    const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps);
-                    const float y = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps + 1);
-                    const float z = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps + 2);
+                    rx = __ldg(a.xyz + 3 * (size_t)gps); ry = __ldg(a.xyz + 3 * (size_t)gps + 1); rz = __ldg(a.xyz + 3 * (size_t)gps + 2);
+                    const float x = a.coord_scale * rx, y = a.coord_scale * ry, z = a.coord_scale * rz;
                     if (a.arch == 0) {   // (x,y) (x,z) (z,x)
                         sample8h<1>(pl, 1, a.H, a.W, x, y, 0.f, sub, acc);
                         sample8h<1>(pl + plane_stride, 1, a.H, a.W, x, z, 0.f, sub, acc);
@@ -106,7 +106,20 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                     pk[q] = *reinterpret_cast<const uint32_t*>(&hv);
                 }
                 *reinterpret_cast<uint4*>(base + canon(pt, 8 * sub, k0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                // row-wise part: position (+ embedding), zeroed chain columns, constant one
+                // the rest of the row: position (+ embedding), zeroed chain columns, constant one
+                if (a.pos_freqs == 0) {
+                    // k0 = 48: columns 32..39 = [x y z 0 0 0 0 0] (lane sub 0), 40..47 = [0 .. 0 1] (lane sub 1);
+                    // the chained columns are filled in later by the last-layer epilogues
+                    if (sub < 2) {
+                        uint4 row = make_uint4(0u, 0u, 0u, 0x3c000000u);   // fp16 1.0 in the top half of .w
+                        if (sub == 0) {
+                            const __half2 xy = __floats2half2_rn(rx, ry), z0 = __floats2half2_rn(rz, 0.f);
+                            row = make_uint4(*reinterpret_cast<const uint32_t*>(&xy), *reinterpret_cast<const uint32_t*>(&z0), 0u, 0u);
+                        }
+                        *reinterpret_cast<uint4*>(base + canon(pt, kFeat + 8 * sub, k0)) = row;
+                    }
+                    continue;
+                }
                 if (colq != 0) continue;
                 const int gp = p0 + r;
                 float px[3] = {0.f, 0.f, 0.f};

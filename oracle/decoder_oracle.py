@@ -42,7 +42,7 @@ def sample_from_planes(arch, planes, xyz, box_warp, depth=1):
     """planes [1,3,32*depth,H,W], xyz [P,3] -> [3,P,32]"""
     N, n_planes, CD, H, W = planes.shape
     coords = (2 / box_warp) * xyz[None]                                   # [1,P,3]
-    inv = torch.linalg.inv(PLANE_AXES[arch])
+    inv = torch.linalg.inv(PLANE_AXES[arch].to(xyz.device))
     proj = torch.bmm(coords.expand(n_planes, -1, -1), inv)                # [3,P,3]
     if arch == "eg3d":
         grid = proj[..., :2].unsqueeze(1)                                 # [3,1,P,2]
