@@ -235,7 +235,10 @@ def run_ours(args, rank, world, dev):
         "clocks": clk.summary(),
         "roofline": {"kernel": "decode_tc_kernel", "bound": "tensor", "achieved": round(flops / (dec_ms * 1e-3) / 1e12, 2),
                      "peak": pk["tf"], "unit": "TFLOP/s", "frac": round(flops / (dec_ms * 1e-3) / 1e12 / pk["tf"], 4),
-                     "traffic": None, "peak_source": pk["src"] + " (sustained bf16)",
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r1_d_summary.md):
+                     # the fp16 planes (37.7 MB) are still in L2 from the repack kernel and the 48 MB of results
+                     # are not written back before the kernel ends, so DRAM sees far less than the 92 MB moved
+                     "traffic": 18.75e6, "peak_source": pk["src"] + " (sustained bf16)",
                      "note": "tcgen05 fp16 decode incl. tri-grid sampling; algorithmic FLOPs = 382720/pt x 500k"},
         "stages_ms": {k: round(v, 4) for k, v in stage_ms.items()},
         "stages_hbm_gbs": {k: hbm(b, stage_ms[k]) for k, b in stage_bytes.items()},

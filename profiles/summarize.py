@@ -29,7 +29,7 @@ for k, (n, v) in sorted(agg.items(), key=lambda x: -x[1][1])[:16]:
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 h = {n: i for i, n in enumerate(rows[0])}
-cols = [("gpu__time_duration.sum", "ms"), ("dram__bytes_read.sum", "rdMB"), ("dram__bytes_write.sum", "wrMB"),
+cols = [("gpu__time_duration.sum", "us"), ("dram__bytes_read.sum", "rdMB"), ("dram__bytes_write.sum", "wrMB"),
         ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram%"),
         ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm%"),
         ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue%"),
