@@ -166,7 +166,12 @@ def run_ours(args, rank, world, dev):
     copy_stream = torch.cuda.Stream(device=dev)
     main_stream = torch.cuda.current_stream()
 
-    def e2e_run(n):
+    # variant: the plane producer keeps fp16 channels-last planes (PackedPlanes) in host memory
+    from gaussian_gan_decoder_b200.decoder_models.fused import PackedPlanes
+    pk_host = [dec.pack_planes(pl).to("cpu").pin_memory() for pl, _ in dev_sets]
+    pk_dev = [PackedPlanes(torch.empty_like(pk_host[0].data, device=dev), pk_host[0].shape) for _ in range(2)]
+
+    def e2e_run(n, packed=False):
         uploaded = [torch.cuda.Event() for _ in range(2)]
         consumed = [torch.cuda.Event() for _ in range(2)]
 
@@ -176,7 +181,10 @@ def run_ours(args, rank, world, dev):
                 if i >= 2:
                     copy_stream.wait_event(consumed[b])
                 pl, xyz = pinned[i % len(pinned)]
-                d_in[b][0].copy_(pl, non_blocking=True)
+                if packed:
+                    pk_dev[b].data.copy_(pk_host[i % len(pk_host)].data, non_blocking=True)
+                else:
+                    d_in[b][0].copy_(pl, non_blocking=True)
                 d_in[b][1].copy_(xyz, non_blocking=True)
                 uploaded[b].record(copy_stream)
 
@@ -186,14 +194,19 @@ def run_ours(args, rank, world, dev):
             if i + 1 < n:
                 upload(i + 1)
             main_stream.wait_event(uploaded[b])
-            dec.G.planes = d_in[b][0]
-            with torch.no_grad():
-                res = dec(z, c, d_in[b][1], 1.0)
-                gm = GaussianModel.from_decoder(res, dec.activated())
-                out = render_simple(cam, gm, bg)
+            if packed:      # streaming caller: sync-free FramePipeline over the C ABI, planes already in kernel layout
+                image = pipe.frame(pk_dev[b], d_in[b][1], cam, bg)
+            else:           # reference-facing classes: decoder.forward -> GaussianModel -> render_simple
+                dec.G.planes = d_in[b][0]
+                with torch.no_grad():
+                    res = dec(z, c, d_in[b][1], 1.0)
+                    gm = GaussianModel.from_decoder(res, dec.activated())
+                    image = render_simple(cam, gm, bg)["render"]
             consumed[b].record(main_stream)
-            img_host[b].copy_(out["render"], non_blocking=True)
+            img_host[b].copy_(image, non_blocking=True)
         torch.cuda.synchronize()
+        if packed:
+            assert not pipe.check()[1], "frame needs to be re-run (capacity / binning mode)"
 
     e2e_run(4)
     barrier()
@@ -202,11 +215,19 @@ def run_ours(args, rank, world, dev):
     e1.record()
     barrier()
     e2e_s = e0.elapsed_time(e1) * 1e-3
+    e2e_run(4, packed=True)
+    barrier()
+    e0.record()
+    e2e_run(args.steps, packed=True)
+    e1.record()
+    barrier()
+    e2e_pk_s = e0.elapsed_time(e1) * 1e-3
+    dec.G.planes = dev_sets[0][0]
 
     if world > 1:
-        t = torch.tensor([ms_total, e2e_s], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms_total, e2e_s, e2e_pk_s], device=dev, dtype=torch.float64)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-        ms_total, e2e_s = t.tolist()
+        ms_total, e2e_s, e2e_pk_s = t.tolist()
     if rank != 0:
         return None
     pk = peaks()
@@ -231,6 +252,11 @@ def run_ours(args, rank, world, dev):
                 "d2h_bytes_per_step": 3 * SIZE * SIZE * 4, "ms_per_step": round(1e3 * e2e_s / args.steps, 3)},
         # planes repack, decode, preprocess, scan, blend + binning: tile scan / scatter / tile sort (mode 2), plus
         # duplicate, 6 digit passes and the range kernel when the radix kernels are enqueued as well (modes 0, 1)
+        # same upload/compute/download loop for a streaming caller: planes kept on the host as fp16 channels-last
+        # (PackedPlanes: half the upload, no repack) and frames enqueued through the sync-free FramePipeline
+        "e2e_packed_planes": {"via": "FramePipeline.frame(PackedPlanes, ...)", "value": round(world * args.steps / e2e_pk_s, 2), "unit": "frames/s",
+                              "h2d_bytes_per_step": pk_host[0].data.numel() + host_sets[0][1].numel() * 4,
+                              "d2h_bytes_per_step": 3 * SIZE * SIZE * 4, "ms_per_step": round(1e3 * e2e_pk_s / args.steps, 3)},
         "gpu_launches": args.steps * {0: 13, 1: 16, 2: 8}[pipe.bin_mode],
         "clocks": clk.summary(),
         "roofline": {"kernel": "decode_tc_kernel", "bound": "tensor", "achieved": round(flops / (dec_ms * 1e-3) / 1e12, 2),

@@ -99,6 +99,8 @@ class FusedDecoderBase(nn.Module):
         flat = self._ensure_flat(feature_planes)
         needs_grad = torch.is_grad_enabled() and (flat.flat.requires_grad or feature_planes.requires_grad or
                                                  any(p.requires_grad for p in self.get_params_custom()[:40]))
+        if needs_grad and isinstance(feature_planes, fused.PackedPlanes):
+            raise RuntimeError("PackedPlanes are inference-only: run under torch.no_grad() or pass the fp32 planes")
         if needs_grad:
             from . import fused_backward
             xyz, scale, rotation, opacity, color = fused_backward.apply(self, feature_planes, init_position)
@@ -111,6 +113,11 @@ class FusedDecoderBase(nn.Module):
         for k in self.ORDER:        # insertion order as in the reference's forward
             result[k] = {"xyz": xyz, "scale": scale, "rotation": rotation, "opacity": opacity, "color": color}[k]
         return result
+
+    def pack_planes(self, feature_planes):
+        """fp32 NCHW planes -> ``fused.PackedPlanes`` (fp16 channels-last), accepted by ``decode`` / ``forward``
+        (when the generator returns it as ``feature_planes``) and by ``FramePipeline.frame`` in place of the tensor."""
+        return fused.pack_planes(self._cfg_for(feature_planes, precision="fp16"), feature_planes)
 
     def activated(self):
         """exp(scale), normalize(rotation), sigmoid(opacity) of the LAST decode, produced by the

@@ -129,8 +129,43 @@ class FlatParams:
         return self.packed
 
 
+class PackedPlanes:
+    """Feature planes already in the layout the tensor-core decoder reads: fp16, channels-last
+    ``[3][D][H][W][32]`` (one texel = one 64-byte half-line).  ``shape`` is the generator's NCHW shape
+    ``(1, 3, 32*D, H, W)`` so the decoder classes can treat it like the tensor it stands for.
+
+    This is the plane-producer handshake of SURVEY 8(f) N3: a generator (or a cache of per-identity
+    planes in host memory) that emits this layout saves the per-latent repack kernel and half of the
+    upload.  Inference only - the backward needs the fp32 planes."""
+    requires_grad = False
+
+    def __init__(self, data, shape):
+        self.data, self.shape = data, tuple(shape)
+
+    def dim(self):
+        return len(self.shape)
+
+    def to(self, device, non_blocking=False):
+        return PackedPlanes(self.data.to(device, non_blocking=non_blocking), self.shape)
+
+    def pin_memory(self):
+        return PackedPlanes(self.data.pin_memory(), self.shape)
+
+
+def pack_planes(cfg, planes_nchw):
+    """fp32 NCHW planes (device) -> PackedPlanes; cfg must be an fp16-precision config."""
+    lib = _lib.load(); _bind(lib)
+    if cfg.precision != 1:
+        raise ValueError("packed planes are the fp16 tensor-core path's layout")
+    planes_nchw = planes_nchw.to(torch.float32).contiguous()
+    data = torch.empty(planes_nchw.numel() * 2, dtype=torch.uint8, device=planes_nchw.device)
+    with torch.cuda.device(planes_nchw.device):
+        _lib.check(lib.ggd_planes_channels_last(_stream(), C.byref(cfg), _lib.ptr(planes_nchw), _lib.ptr(data)))
+    return PackedPlanes(data, planes_nchw.shape)
+
+
 def decode_forward(cfg, planes_nchw, xyz, packed, with_activations=True):
-    """planes [1,3,32*D,H,W] fp32 (generator layout), xyz [P,3] -> dict of raw attributes
+    """planes [1,3,32*D,H,W] fp32 (generator layout) or PackedPlanes, xyz [P,3] -> dict of raw attributes
     (+ activated scale/rotation/opacity for the rasteriser)."""
     lib = _lib.load(); _bind(lib)
     if not xyz.is_cuda:
@@ -139,7 +174,14 @@ def decode_forward(cfg, planes_nchw, xyz, packed, with_activations=True):
     P = xyz.shape[0]
     if planes_nchw.dim() != 5 or planes_nchw.shape[0] != 1 or planes_nchw.shape[1] != 3:
         raise ValueError(f"feature_planes must be [1,3,C*D,H,W], got {tuple(planes_nchw.shape)}")
-    planes_nchw = planes_nchw.to(device=dev, dtype=torch.float32).contiguous()
+    prepacked = isinstance(planes_nchw, PackedPlanes)
+    if prepacked:
+        if cfg.precision != 1:
+            raise ValueError("PackedPlanes need the fp16 decoder (decoder.precision = 'fp16')")
+        if not planes_nchw.data.is_cuda:
+            raise RuntimeError("PackedPlanes must be on the GPU: the decoder has no CPU path")
+    else:
+        planes_nchw = planes_nchw.to(device=dev, dtype=torch.float32).contiguous()
     xyz = xyz.to(torch.float32).contiguous()
     new = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
     out = dict(xyz=new(P, 3), scale=new(P, 3), rotation=new(P, 4), opacity=new(P, 1), color=new(P, 3))
@@ -149,8 +191,11 @@ def decode_forward(cfg, planes_nchw, xyz, packed, with_activations=True):
     p = _lib.ptr
     with torch.cuda.device(dev):
         s = _stream()
-        planes_cl = torch.empty(planes_nchw.numel() * (2 if cfg.precision == 1 else 4), dtype=torch.uint8, device=dev)
-        _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(planes_cl)))
+        if prepacked:
+            planes_cl = planes_nchw.data
+        else:
+            planes_cl = torch.empty(planes_nchw.numel() * (2 if cfg.precision == 1 else 4), dtype=torch.uint8, device=dev)
+            _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(planes_cl)))
         _lib.check(lib.ggd_decode_forward(s, C.byref(cfg), p(planes_cl), p(xyz), P, p(packed),
                                           p(out["xyz"]), p(out["scale"]), p(out["rotation"]), p(out["opacity"]),
                                           p(out["color"]), p(act.get("act_scale")), p(act.get("act_rotation")),

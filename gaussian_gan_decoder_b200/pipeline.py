@@ -50,12 +50,16 @@ class FramePipeline:
         flat = self.dec._ensure_flat(planes_nchw)
         cfg = self.dec._cfg_for(planes_nchw)
         packed = flat.packed_weights()
-        nbytes = planes_nchw.numel() * (2 if cfg.precision == 1 else 4)
-        if self.planes_cl is None or self.planes_cl.numel() != nbytes:
-            self.planes_cl = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
         s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(self.planes_cl)))
-        _lib.check(lib.ggd_decode_forward(s, C.byref(cfg), p(self.planes_cl), p(xyz), P, p(packed),
+        if isinstance(planes_nchw, fused.PackedPlanes):      # producer already emits the kernel's layout
+            planes_cl = planes_nchw.data
+        else:
+            nbytes = planes_nchw.numel() * (2 if cfg.precision == 1 else 4)
+            if self.planes_cl is None or self.planes_cl.numel() != nbytes:
+                self.planes_cl = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
+            planes_cl = self.planes_cl
+            _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(planes_cl)))
+        _lib.check(lib.ggd_decode_forward(s, C.byref(cfg), p(planes_cl), p(xyz), P, p(packed),
                                           p(self.out["xyz"]), p(self.out["scale"]), p(self.out["rotation"]),
                                           p(self.out["opacity"]), p(self.out["color"]),
                                           p(self.act["scale"]), p(self.act["rotation"]), p(self.act["opacity"])))

@@ -98,12 +98,15 @@ class SyntheticGenerator(torch.nn.Module):
         if arch == "panohead":
             self.rendering_kwargs["triplane_depth"] = depth
         self.renderer = _Renderer()
-        self.calls = []
+        self.calls = {}          # last camera tensor each entry point received (no host sync here)
+        self._ws = None
 
     def mapping(self, z, c, truncation_psi=1):
-        self.calls.append(("mapping", float(c.abs().sum())))
-        return torch.zeros(1, 14, 512, device=z.device)
+        self.calls["mapping"] = c
+        if self._ws is None or self._ws.device != z.device:
+            self._ws = torch.zeros(1, 14, 512, device=z.device)
+        return self._ws
 
     def synthesis(self, ws, c, noise_mode="const"):
-        self.calls.append(("synthesis", float(c.abs().sum())))
+        self.calls["synthesis"] = c
         return {"feature_planes": self.planes}

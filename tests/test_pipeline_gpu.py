@@ -51,3 +51,34 @@ def synthetic_cam(dev, h_off):
     for k in ("world_view_transform", "full_proj_transform", "camera_center"):
         setattr(cam, k, getattr(cam, k).contiguous().to(dev))
     return cam
+
+
+def test_packed_planes_handshake(cuda):
+    """A plane producer may hand over fp16 channels-last planes (PackedPlanes, also via pinned host memory):
+    same attributes and image as the fp32 NCHW route, without the repack kernel."""
+    g = synthetic.gen(9)
+    planes = synthetic.planes("panohead", g, res=64, depth=3).to(cuda)
+    xyz = synthetic.head_shell_points(20_000, g).to(cuda)
+    torch.manual_seed(3)
+    dec = SequentialDecoderReverse(StubG(planes, "panohead", 3), use_xyz_embedding=False, use_gen_finetune=False, device=cuda)
+    cam = synthetic_cam(cuda, 0.0)
+    bg = torch.tensor(synthetic.BG["panohead"], device=cuda)
+    z, c = torch.zeros(1, 512, device=cuda), torch.zeros(1, 25, device=cuda)
+    with torch.no_grad():
+        ref = dec(z, c, xyz, 1.0)
+    packed = dec.pack_planes(planes)
+    assert packed.shape == tuple(planes.shape) and packed.data.numel() == planes.numel() * 2
+    host = packed.to("cpu").pin_memory()
+    dec.G.planes = host.to(cuda, non_blocking=True)            # the generator now "emits" packed planes
+    with torch.no_grad():
+        res = dec(z, c, xyz, 1.0)
+    for k in ("xyz", "scale", "rotation", "opacity", "color"):
+        assert torch.equal(res[k], ref[k]), k
+    pipe = FramePipeline(dec, 20_000, 256, cuda)
+    a = pipe.frame(planes, xyz, cam, bg).clone()
+    b = pipe.frame(dec.G.planes, xyz, cam, bg).clone()
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
+    xyz_g = xyz.clone().requires_grad_(False)
+    with pytest.raises(RuntimeError):
+        dec(z, c, xyz_g, 1.0)                                    # parameters require grad and grad mode is on
