@@ -79,10 +79,12 @@ struct GeomState {
     uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched
     uint8_t* clamped;         // [P][3]
     uint32_t* counters;       // [0] num_rendered, [1] overflow flag, [2] scan ticket, [3] clamped count,
-                              // [4] 1 = this frame is binned per tile (tile_binning.cu), [5] longest tile list
+                              // [4] 1 = this frame is binned per tile (tile_binning.cu), [5] longest tile list,
+                              // [6] element count the radix kernels see, [7] number of tile lists > kTileSortMax
     uint64_t* scan_status;    // [scan tiles] decoupled look-back words of the scan
-    uint32_t* tile_counts;    // [tiles][kTileCountStride] instances per tile, counted by preprocess; one 128-byte line
-                              // per tile so the atomics spread over the L2 slices (last field: size depends on W, H)
+    uint32_t* tile_counts;    // [tiles][kTileCountStride] word 0: instances per tile, counted by preprocess; word 2: the
+                              // tile's write cursor; word 1 of entry i: id of the i-th long tile list.  One 128-byte
+                              // line per tile so the atomics spread over the L2 slices (last field: size depends on W, H)
     size_t bytes;
 };
 struct BinState {
@@ -139,7 +141,8 @@ int launch_tile_ranges(cudaStream_t s, const GeomState& g, const BinState& b, ui
                        const ImgState& im, int tiles, const uint32_t* skip = nullptr);
 // per-tile binning (tile_binning.cu)
 constexpr uint32_t kTileCountStride = 32;  // words between two tiles' counters
-constexpr uint32_t kTileSortMax = 4096;   // longest tile list the shared-memory sort takes
+constexpr uint32_t kTileSortMax = 4096;   // longest tile list the register-resident shared-memory sort takes
+constexpr uint32_t kTileSortLargeMax = 24576;   // longest list of the one-CTA-per-SM variant (192 KB of words + 32 KB of buckets)
 int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int tiles, uint64_t capacity, int P, bool strict);
 int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g, const int* radii,
                         const BinState& b, const ImgState& im, uint64_t capacity);

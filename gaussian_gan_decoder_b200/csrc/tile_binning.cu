@@ -14,14 +14,16 @@
 // segment and sorted where it lands:
 //   preprocess        counts instances per tile (atomics, fused into the projection kernel)
 //   tile_scan_kernel  exclusive scan of the counts -> ranges[tile] = [start, end) ((0,0) for an empty
-//                     tile, as the reference leaves it); turns each counter into the tile's write
-//                     cursor; decides whether the frame qualifies (longest list <= kTileSortMax,
+//                     tile, as the reference leaves it); sets up each tile's write cursor; decides
+//                     whether the frame qualifies (longest list <= kTileSortMax,
 //                     R <= capacity)
 //   tile_scatter      slot-centric like duplicate_kernel; claims a slot in the tile's segment with an
 //                     atomic on the tile's cursor
 //   tile_sort_kernel  one CTA per tile: distribution sort of the 64-bit words in shared memory (bitonic
 //                     network for lists with heavily clustered depths)
-// Frames that do not qualify (a tile list longer than kTileSortMax) take the radix path of binning.cu;
+//   tile_sort_large_kernel  the same for lists of 4097..24576 instances: persistent CTAs of 1024 threads,
+//                     one per SM, walk the list of long tiles the scan wrote
+// Frames that do not qualify (a tile list longer than kTileSortLargeMax) take the radix path of binning.cu;
 // the decision is made on the device (counters[4]) and both sets of kernels are always enqueued, the
 // ones that do not apply return at once, so no host round trip is needed.
 #include "common.cuh"
@@ -36,7 +38,7 @@ tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int 
                  const uint32_t* __restrict__ offsets, int P, uint32_t* __restrict__ counters, int strict)
 {
     __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_max, s_carry;
+    __shared__ uint32_t s_max, s_carry, s_large;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     uint32_t mx = 0;
     for (int i = t; i < tiles; i += kScanThreadsT) mx = max(mx, counts[(size_t)i * kTileCountStride]);
@@ -48,9 +50,10 @@ tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int 
         uint32_t m = 0;
         for (int w = 0; w < kScanThreadsT / 32; ++w) m = max(m, s_warp[w]);
         const uint32_t R = P > 0 ? __ldg(offsets + P - 1) : 0u;
-        const bool per_tile = m <= kTileSortMax && R <= capacity;
+        const bool per_tile = m <= kTileSortLargeMax && R <= capacity;
         s_max = per_tile ? 1u : 0u;
         s_carry = 0;
+        s_large = 0;
         // flag 1: more instances than the buffers hold; flag 2: the caller enqueued no radix kernels but this
         // frame needs them.  Either way the image is undefined and the caller runs the stage again.
         counters[1] = ((R > capacity) ? 1u : 0u) | ((strict && !per_tile) ? 2u : 0u);
@@ -82,12 +85,15 @@ tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int 
         if (i < tiles) {
             const uint32_t start = off + incl - v;
             ranges[i] = v ? make_uint2(start, start + v) : make_uint2(0u, 0u);
-            counts[(size_t)i * kTileCountStride] = start;   // from here on: the tile's write cursor
+            counts[(size_t)i * kTileCountStride + 2] = start;   // the tile's write cursor (word 0 keeps the count, so
+                                                                // stage 2 can be run again on the same geometry state)
+            if (v > kTileSortMax) counts[(size_t)atomicAdd(&s_large, 1u) * kTileCountStride + 1] = (uint32_t)i;
         }
         __syncthreads();
         if (t == kScanThreadsT - 1) s_carry = off + incl;
         __syncthreads();
     }
+    if (t == 0) counters[7] = s_large;
 }
 
 constexpr int kScatterThreads = 256;
@@ -145,7 +151,7 @@ tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ me
         const uint32_t depth = s_depth[g], id = (uint32_t)(base + g);
         keys_unsorted[s] = ((uint64_t)tile << 32) | depth;
         vals_unsorted[s] = id;
-        const uint32_t pos = atomicAdd(cursors + (size_t)tile * kTileCountStride, 1u);
+        const uint32_t pos = atomicAdd(cursors + (size_t)tile * kTileCountStride + 2, 1u);
         words[pos] = ((uint64_t)depth << 32) | id;
     }
 }
@@ -219,13 +225,56 @@ __device__ __forceinline__ void sort_tile(uint64_t* __restrict__ s, const uint64
     }
 }
 
-// Distribution sort of one tile list (n <= 256 E words, thread t holds words t, t + 256, ...): the depth
-// bits of a tile's instances are spread over a narrow interval, so a monotone map of [min, max] onto 256 E
-// buckets leaves about one word per bucket.  Words are dropped into their bucket (shared-memory atomics
+// Distribution sort of one tile list (n <= 256 E words, thread t holds words t, t + 256, ...): a monotone map
+// of the list's depth interval onto 256 E buckets (BucketMap below) leaves about one word per bucket.  Words are dropped into their bucket (shared-memory atomics
 // hand out the rank inside the bucket), bucket starts come from one scan, and the thread owning a bucket
 // orders its few words by insertion.  O(n) instead of the bitonic network's O(n log^2 n); a list with an
 // overfull bucket (many equal or clustered depths) falls back to the network.
 constexpr uint32_t kMaxBucket = 16;
+
+// Monotone map of a list's depth bits onto n_b buckets that evens out the bucket loads: a coarse histogram
+// (kCoarse bins, linear between the list's min and max) gives a piecewise-linear estimate of the depth CDF,
+// and a word goes to bucket  n_b / n * (words below its coarse bin + its fraction of that bin).  Depths on a
+// head cluster at the front and the back surface; a plain linear map would pile them into a few buckets.
+constexpr int kCoarse = 128;
+struct BucketMap {
+    uint32_t dmin;
+    float scale_c, ratio;            // coarse bins per depth unit, n_b / n
+    const uint32_t* cstart;          // [kCoarse + 1] exclusive prefix of the coarse counts (shared memory)
+    uint32_t n_b;
+    __device__ __forceinline__ uint32_t coarse(uint32_t d) const
+    {
+        return min((uint32_t)(kCoarse - 1), (uint32_t)((float)(d - dmin) * scale_c));
+    }
+    __device__ __forceinline__ uint32_t operator()(uint32_t d) const
+    {
+        const float x = (float)(d - dmin) * scale_c;
+        const uint32_t kc = min((uint32_t)(kCoarse - 1), (uint32_t)x);
+        const float below = (float)cstart[kc], in_bin = (float)(cstart[kc + 1] - cstart[kc]);
+        return min(n_b - 1u, (uint32_t)((below + (x - (float)kc) * in_bin) * ratio));
+    }
+};
+// exclusive scan of s_c[0..kCoarse) into s_cstart[0..kCoarse], by warp 0 (call with all threads, then sync)
+__device__ __forceinline__ void coarse_scan(const uint32_t* __restrict__ s_c, uint32_t* __restrict__ s_cstart)
+{
+    if (threadIdx.x < 32) {
+        constexpr int kPerLane = kCoarse / 32;
+        const int lane = threadIdx.x;
+        uint32_t v[kPerLane], sum = 0;
+#pragma unroll
+        for (int q = 0; q < kPerLane; ++q) { v[q] = s_c[lane * kPerLane + q]; sum += v[q]; }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += u;
+        }
+        uint32_t run = incl - sum;
+#pragma unroll
+        for (int q = 0; q < kPerLane; ++q) { s_cstart[lane * kPerLane + q] = run; run += v[q]; }
+        if (lane == 31) s_cstart[kCoarse] = run;
+    }
+}
 
 template <int E>
 __device__ __forceinline__ void dist_sort_tile(uint64_t* __restrict__ s_out, uint32_t* __restrict__ s_hist,
@@ -235,9 +284,11 @@ __device__ __forceinline__ void dist_sort_tile(uint64_t* __restrict__ s_out, uin
     constexpr uint32_t n_b = kTileSortThreads * E;
     __shared__ uint32_t s_red[2][kTileSortThreads / 32];
     __shared__ uint32_t s_part[kTileSortThreads / 32];
+    __shared__ uint32_t s_c[kCoarse], s_cstart[kCoarse + 1];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     uint64_t w[E];
     uint32_t dmin = 0xffffffffu, dmax = 0u;
+    if (t < kCoarse) s_c[t] = 0;
 #pragma unroll
     for (int r = 0; r < E; ++r) {
         const uint32_t i = t + r * kTileSortThreads;
@@ -254,14 +305,20 @@ __device__ __forceinline__ void dist_sort_tile(uint64_t* __restrict__ s_out, uin
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < kTileSortThreads / 32; ++k) { dmin = min(dmin, s_red[0][k]); dmax = max(dmax, s_red[1][k]); }
-    const float scale = (float)n_b / ((float)(dmax - dmin) + 1.0f);
+    BucketMap map{dmin, (float)kCoarse / ((float)(dmax - dmin) + 1.0f), (float)n_b / (float)n, s_cstart, n_b};
+#pragma unroll
+    for (int r = 0; r < E; ++r)
+        if (t + r * kTileSortThreads < n) atomicAdd(&s_c[map.coarse((uint32_t)(w[r] >> 32))], 1u);
+    __syncthreads();
+    coarse_scan(s_c, s_cstart);
+    __syncthreads();
     uint32_t bk[E];   // bucket | rank inside the bucket << 16
 #pragma unroll
     for (int r = 0; r < E; ++r) {
         const uint32_t i = t + r * kTileSortThreads;
         bk[r] = 0;
         if (i < n) {
-            const uint32_t b = min(n_b - 1u, (uint32_t)((float)((uint32_t)(w[r] >> 32) - dmin) * scale));
+            const uint32_t b = map((uint32_t)(w[r] >> 32));
             bk[r] = b | (atomicAdd(&s_hist[b], 1u) << 16);
         }
     }
@@ -328,12 +385,145 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ 
     const uint32_t tile = blockIdx.x;
     const uint2 range = ranges[tile];
     const uint32_t n = range.y - range.x;
-    if (n == 0) return;
+    if (n == 0 || n > kTileSortMax) return;   // long lists: tile_sort_large_kernel
     if (n <= 256) dist_sort_tile<1>(s, h, words, range.x, n, tile, keys, vals);
     else if (n <= 512) dist_sort_tile<2>(s, h, words, range.x, n, tile, keys, vals);
     else if (n <= 1024) dist_sort_tile<4>(s, h, words, range.x, n, tile, keys, vals);
     else if (n <= 2048) dist_sort_tile<8>(s, h, words, range.x, n, tile, keys, vals);
     else dist_sort_tile<16>(s, h, words, range.x, n, tile, keys, vals);
+}
+
+// Long tile lists (kTileSortMax < n <= kTileSortLargeMax): same distribution sort, but the list stays in
+// global memory (L2) for two streaming passes instead of registers, one CTA of 1024 threads owns a whole
+// SM's shared memory, and an overfull bucket is sorted in place by the CTA with a comparison network.
+constexpr int kLargeThreads = 1024;
+constexpr uint32_t kLargeBuckets = 8192;
+constexpr uint32_t kLargeInsertMax = 32;   // buckets up to this size are ordered by their owner thread
+
+// ascending bitonic network on s[0..m) by the whole CTA ("normalised" form: every compare-exchange puts the
+// smaller word first, the first step of a phase mirrors, so positions >= m can be treated as +infinity)
+__device__ void cta_sort_range(uint64_t* __restrict__ s, uint32_t m)
+{
+    uint32_t m_pad = 2;
+    while (m_pad < m) m_pad <<= 1;
+    for (uint32_t k = 2; k <= m_pad; k <<= 1) {
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t i = threadIdx.x; i < (m_pad >> 1); i += kLargeThreads) {
+                const uint32_t lo = ((i & ~(j - 1)) << 1) | (i & (j - 1));
+                const uint32_t hi = (j == (k >> 1)) ? (lo ^ (k - 1)) : (lo | j);   // mirrored partner in the first step
+                if (hi < m) {
+                    const uint64_t a = s[lo], b = s[hi];
+                    if (a > b) { s[lo] = b; s[hi] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kLargeThreads, 1)
+tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ words, uint64_t* __restrict__ keys,
+                       uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters, const uint32_t* __restrict__ tile_list)
+{
+    if (__ldg(counters + 4) == 0u) return;
+    extern __shared__ __align__(16) uint8_t s_dyn[];
+    uint64_t* s_out = reinterpret_cast<uint64_t*>(s_dyn);                                      // [kTileSortLargeMax]
+    uint32_t* s_hist = reinterpret_cast<uint32_t*>(s_dyn + sizeof(uint64_t) * kTileSortLargeMax);   // [kLargeBuckets]
+    __shared__ uint32_t s_red[2][kLargeThreads / 32];
+    __shared__ uint32_t s_part[kLargeThreads / 32];
+    __shared__ uint32_t s_big[64], s_nbig;
+    __shared__ uint32_t s_c[kCoarse], s_cstart[kCoarse + 1];
+    constexpr int kPer = kLargeBuckets / kLargeThreads;   // buckets per thread
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t n_large = __ldg(counters + 7);
+    for (uint32_t li = blockIdx.x; li < n_large; li += gridDim.x) {
+        const uint32_t tile = __ldg(tile_list + (size_t)li * kTileCountStride + 1);
+        const uint2 range = ranges[tile];
+        const uint32_t n = range.y - range.x;
+        const uint64_t* src = words + range.x;
+        // depth interval of the list
+        uint32_t dmin = 0xffffffffu, dmax = 0u;
+        for (uint32_t i = t; i < n; i += kLargeThreads) {
+            const uint32_t d = (uint32_t)(__ldg(src + i) >> 32);
+            dmin = min(dmin, d); dmax = max(dmax, d);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            dmin = min(dmin, __shfl_xor_sync(0xffffffffu, dmin, o));
+            dmax = max(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+        }
+        if (lane == 0) { s_red[0][warp] = dmin; s_red[1][warp] = dmax; }
+        for (uint32_t i = t; i < kLargeBuckets; i += kLargeThreads) s_hist[i] = 0;
+        if (t == 0) s_nbig = 0;
+        if (t < kCoarse) s_c[t] = 0;
+        __syncthreads();
+        for (int k = 0; k < kLargeThreads / 32; ++k) { dmin = min(dmin, s_red[0][k]); dmax = max(dmax, s_red[1][k]); }
+        BucketMap map{dmin, (float)kCoarse / ((float)(dmax - dmin) + 1.0f), (float)kLargeBuckets / (float)n, s_cstart, kLargeBuckets};
+        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_c[map.coarse((uint32_t)(__ldg(src + i) >> 32))], 1u);
+        __syncthreads();
+        coarse_scan(s_c, s_cstart);
+        __syncthreads();
+        auto bucket = [&](uint64_t w) { return map((uint32_t)(w >> 32)); };
+        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_hist[bucket(__ldg(src + i))], 1u);
+        __syncthreads();
+        // exclusive scan; thread t owns buckets [t kPer, (t + 1) kPer)
+        uint32_t cnt[kPer], sum = 0;
+#pragma unroll
+        for (int q = 0; q < kPer; ++q) { cnt[q] = s_hist[t * kPer + q]; sum += cnt[q]; }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_part[warp] = incl;
+        __syncthreads();
+        uint32_t start = incl - sum;
+        for (int k = 0; k < warp; ++k) start += s_part[k];
+        {
+            uint32_t run = start;
+#pragma unroll
+            for (int q = 0; q < kPer; ++q) { s_hist[t * kPer + q] = run; run += cnt[q]; }
+        }
+        __syncthreads();
+        for (uint32_t i = t; i < n; i += kLargeThreads) {
+            const uint64_t w = __ldg(src + i);
+            s_out[atomicAdd(&s_hist[bucket(w)], 1u)] = w;
+        }
+        __syncthreads();
+        {
+            uint32_t b0 = start;
+#pragma unroll
+            for (int q = 0; q < kPer; ++q) {
+                const uint32_t m = cnt[q];
+                if (m > kLargeInsertMax) {
+                    const uint32_t slot = atomicAdd(&s_nbig, 1u);
+                    if (slot < 32) { s_big[2 * slot] = b0; s_big[2 * slot + 1] = m; }
+                } else {
+                    for (uint32_t i = 1; i < m; ++i) {
+                        const uint64_t x = s_out[b0 + i];
+                        uint32_t j = i;
+                        while (j > 0 && s_out[b0 + j - 1] > x) { s_out[b0 + j] = s_out[b0 + j - 1]; --j; }
+                        s_out[b0 + j] = x;
+                    }
+                }
+                b0 += m;
+            }
+        }
+        __syncthreads();
+        const uint32_t nbig = s_nbig;
+        if (nbig > 32) {
+            cta_sort_range(s_out, n);                     // hopelessly clustered: sort the whole list
+        } else {
+            for (uint32_t k = 0; k < nbig; ++k) cta_sort_range(s_out + s_big[2 * k], s_big[2 * k + 1]);
+        }
+        for (uint32_t i = t; i < n; i += kLargeThreads) {
+            const uint64_t x = s_out[i];
+            vals[range.x + i] = (uint32_t)x;
+            keys[range.x + i] = ((uint64_t)tile << 32) | (x >> 32);
+        }
+        __syncthreads();
+    }
 }
 
 }  // namespace
@@ -364,6 +554,13 @@ int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, cons
     GGD_CUDA_CHECK(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     tile_sort_kernel<<<tiles, kTileSortThreads, smem, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters);
     GGD_LAUNCH_CHECK("tile_sort_kernel");
+    constexpr int smem_large = (int)(sizeof(uint64_t) * kTileSortLargeMax + sizeof(uint32_t) * kLargeBuckets);
+    GGD_CUDA_CHECK(cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_large));
+    int sms = 148;
+    { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    tile_sort_large_kernel<<<std::min(tiles, sms), kLargeThreads, smem_large, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters,
+                                                                                  g.tile_counts);
+    GGD_LAUNCH_CHECK("tile_sort_large_kernel");
     return GGD_OK;
 }
 

@@ -118,4 +118,6 @@ class FramePipeline:
                 self.bin_mode, over = 1, True
             elif self.bin_mode == 1 and info[0] and not over:
                 self.bin_mode = 2
+            elif self.bin_mode == 1 and not info[0] and not over:
+                self.bin_mode = 0       # tile lists too long for the per-tile path: stop counting per tile
         return R, over

@@ -110,41 +110,59 @@ class _CNamespace:
         p = _lib.ptr
         key = (dev.index, P, H, W)
         hint = _capacity_hint.get(key)
+        # Stage-2 binning (ggd_raster_binning): counting instances per tile costs one atomic per (splat, tile),
+        # wasted on frames whose tile lists are too long for the per-tile path.  Remember per shape whether
+        # the last frame qualified; a shape that did not is rendered radix-only and probed again now and then.
+        lib_mode = lib.ggd_raster_binning(-1)
+        bh = _binning_hint.setdefault(key, [min(lib_mode, 1), 0])
+        mode = bh[0] if lib_mode else 0
+        if mode == 0 and lib_mode != 0:
+            bh[1] += 1
+            if bh[1] % 64 == 0:
+                mode = 1
+        lib.ggd_raster_binning(mode)
         pinned = _pinned_u32(dev)
         host_R = C.c_void_p(pinned.data_ptr())
-        with torch.cuda.device(dev):
-            s = _stream()
-            geom_b, _, img_b = workspace_sizes(P, W, H, 0)
-            geom = torch.empty(geom_b, dtype=torch.uint8, device=dev)
-            img = torch.empty(img_b, dtype=torch.uint8, device=dev)
-            pre_args = (s, P, int(degree), M, W, H, p(means3D), p(sh), p(colors), p(opacity), p(scales),
-                        float(scale_modifier), p(rotations), p(cov3D_precomp), p(viewmatrix), p(projmatrix),
-                        p(campos), float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
-                        p(geom), p(radii), host_R)
+        try:
+            with torch.cuda.device(dev):
+                s = _stream()
+                geom_b, _, img_b = workspace_sizes(P, W, H, 0)
+                geom = torch.empty(geom_b, dtype=torch.uint8, device=dev)
+                img = torch.empty(img_b, dtype=torch.uint8, device=dev)
+                pre_args = (s, P, int(degree), M, W, H, p(means3D), p(sh), p(colors), p(opacity), p(scales),
+                            float(scale_modifier), p(rotations), p(cov3D_precomp), p(viewmatrix), p(projmatrix),
+                            p(campos), float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
+                            p(geom), p(radii), host_R)
 
-            def render(cap):
-                binning = torch.empty(workspace_sizes(P, W, H, cap)[1], dtype=torch.uint8, device=dev)
-                _lib.check(lib.ggd_raster_render(s, P, W, H, p(background), p(colors), p(radii), p(geom),
-                                                 p(binning), cap, p(img), p(out_color)))
-                return binning
+                def render(cap):
+                    binning = torch.empty(workspace_sizes(P, W, H, cap)[1], dtype=torch.uint8, device=dev)
+                    _lib.check(lib.ggd_raster_render(s, P, W, H, p(background), p(colors), p(radii), p(geom),
+                                                     p(binning), cap, p(img), p(out_color)))
+                    return binning
 
-            _lib.check(lib.ggd_raster_preprocess(*pre_args))
-            if hint is None:
-                torch.cuda.current_stream().synchronize()       # first frame of this shape only
-                R = int(pinned[0].item()) & 0xffffffff
-                cap = max(R, 1)
-                binning = render(cap)
-            else:
-                cap = hint
-                binning = render(cap)
-                torch.cuda.current_stream().synchronize()       # end of frame, nothing queued behind it
-                R = int(pinned[0].item()) & 0xffffffff
-                if R > cap:                                     # guess too small: redo binning + blend
-                    cap = R
+                _lib.check(lib.ggd_raster_preprocess(*pre_args))
+                if hint is None:
+                    torch.cuda.current_stream().synchronize()       # first frame of this shape only
+                    R = int(pinned[0].item()) & 0xffffffff
+                    cap = max(R, 1)
                     binning = render(cap)
-            if debug:
-                torch.cuda.current_stream().synchronize()
-            _capacity_hint[key] = max(int(R * 1.25) + 4096, 4096)
+                else:
+                    cap = hint
+                    binning = render(cap)
+                    torch.cuda.current_stream().synchronize()       # end of frame, nothing queued behind it
+                    R = int(pinned[0].item()) & 0xffffffff
+                    if R > cap:                                     # guess too small: redo binning + blend
+                        cap = R
+                        binning = render(cap)
+                if debug:
+                    torch.cuda.current_stream().synchronize()
+                _capacity_hint[key] = max(int(R * 1.25) + 4096, 4096)
+                if mode:
+                    info = (C.c_uint32 * 2)()
+                    _lib.check(lib.ggd_raster_binning_info(s, p(geom), P, info))
+                    bh[0] = 1 if info[0] else 0
+        finally:
+            lib.ggd_raster_binning(lib_mode)
         # capacity travels with the buffer so backward can re-carve it
         binning.ggd_capacity = cap
         return R, out_color, radii, geom, binning, img
@@ -169,6 +187,7 @@ class _CNamespace:
 
 
 _C = _CNamespace()
+_binning_hint = {}
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,

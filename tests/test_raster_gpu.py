@@ -268,7 +268,8 @@ def test_mark_visible(cuda):
 
 @pytest.mark.parametrize("P,size,trained,expect_per_tile", [
     (257, 100, True, True), (50000, 512, False, True), (500_000, 512, False, True),
-    (400_000, 64, True, False),      # 16 tiles only: lists far longer than the shared-memory sort takes
+    (500_000, 512, True, True),      # trained-like splats: tile lists of 5-10k instances (long-list kernel)
+    (400_000, 64, True, False),      # 16 tiles only: lists far longer than the shared-memory sorts take
 ])
 def test_binning_modes_agree(cuda, P, size, trained, expect_per_tile):
     """Per-tile binning (tile_binning.cu) and the global radix sort give the same bits; the per-frame choice
@@ -284,7 +285,7 @@ def test_binning_modes_agree(cuda, P, size, trained, expect_per_tile):
         info = (C.c_uint32 * 2)()
         _lib.check(lib.ggd_raster_binning_info(None, C.c_void_p(auto["_buffers"][0].data_ptr()), P, info))
         assert bool(info[0]) == expect_per_tile, (info[0], info[1])
-        assert (info[1] <= 4096) == expect_per_tile
+        assert (info[1] <= 24576) == expect_per_tile
         lib.ggd_raster_binning(0)
         radix = run_ours(s, cuda)
     finally:
@@ -295,11 +296,12 @@ def test_binning_modes_agree(cuda, P, size, trained, expect_per_tile):
     assert int(counts.sum()) == auto["R"]
 
 
-def test_binning_clustered_depths(cuda):
+@pytest.mark.parametrize("P,longest_at_least", [(60_000, 64), (400_000, 4097)])
+def test_binning_clustered_depths(cuda, P, longest_at_least):
     """All splats at (nearly) one depth: every tile list collapses into a few buckets of the distribution
-    sort, which must hand over to its comparison network; ties in depth are ordered by Gaussian index."""
+    sort, which must hand over to its comparison network; ties in depth are ordered by Gaussian index.
+    The second size puts the lists into the long-list kernel."""
     lib = _lib.load()
-    P = 60_000
     s = synthetic.raster_scene(P, size=256, seed_offset=3)
     V = s["viewmatrix"]
     d = V[:3, 2] / V[:3, 2].norm()
@@ -310,7 +312,7 @@ def test_binning_clustered_depths(cuda):
         auto = run_ours(s, cuda)
         info = (C.c_uint32 * 2)()
         _lib.check(lib.ggd_raster_binning_info(None, C.c_void_p(auto["_buffers"][0].data_ptr()), P, info))
-        assert info[0] == 1 and info[1] > 64
+        assert info[0] == 1 and info[1] >= longest_at_least, (info[0], info[1])
         lib.ggd_raster_binning(0)
         radix = run_ours(s, cuda)
     finally:
@@ -319,3 +321,24 @@ def test_binning_clustered_depths(cuda):
     depth_bits = auto["point_list_keys"] & 0xffffffff
     assert depth_bits.unique().numel() < 64            # the scene really is degenerate in depth
     assert_bit_exact(auto, radix, P)
+
+
+def test_stage2_rerun_on_same_geometry_state(cuda):
+    """ggd_raster_render may be called again on the state ggd_raster_preprocess left (the binding does that
+    after a capacity overflow; a caller may do it to change the background): same image, in both binning modes."""
+    lib = _lib.load()
+    P, size = 20_000, 160
+    s = to_dev(synthetic.raster_scene(P, size=size, seed_offset=4), cuda)
+    p = _lib.ptr
+    for mode in (1, 0):
+        prev = lib.ggd_raster_binning(mode)
+        try:
+            first = run_ours(s, cuda)
+            geom, binning, img = first["_buffers"]
+            again = torch.zeros_like(first["out_color"])
+            _lib.check(lib.ggd_raster_render(None, P, size, size, p(s["bg"]), None, p(first["radii"]), p(geom), p(binning),
+                                             first["capacity"], p(img), p(again)))
+            torch.cuda.synchronize()
+        finally:
+            lib.ggd_raster_binning(prev)
+        assert torch.equal(again, first["out_color"])
