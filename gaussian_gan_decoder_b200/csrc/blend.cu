@@ -57,10 +57,13 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
              uint32_t* __restrict__ n_contrib, const float* __restrict__ bg,
              float* __restrict__ out_color)
 {
-    __shared__ float4 s_a[kBatch];  // x, y, conic.x, conic.y
-    __shared__ float4 s_b[kBatch];  // conic.z, opacity, r, g
-    __shared__ float s_c[kBatch];   // b
+    __shared__ __align__(16) float4 s_rec[3 * kBatch];  // per instance: {x, y, conic.x, conic.y}, {conic.z, opacity, r, g}, {b, -, -, -}
     __shared__ uint32_t s_mask[kBatch];
+    // 32-bit shared-window addresses, formed once: inside the list walk the compiler would otherwise rebuild the
+    // generic -> shared conversion for every record it touches (8 of the loop's 68 instructions)
+    // (the mov keeps ptxas from re-materialising the conversion inside the loop)
+    uint32_t rec_addr;
+    asm volatile("mov.u32 %0, %1;" : "=r"(rec_addr) : "r"((uint32_t)__cvta_generic_to_shared(s_rec)));
 
     const uint32_t tiles_x = (W + kTileX - 1) / kTileX;
     const int tr = threadIdx.x, warp = tr >> 5, lane = tr & 31;
@@ -71,7 +74,10 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
     const float fx = (float)px, fy = (float)py;
     const float tile_x0 = (float)(blockIdx.x * kTileX), tile_y0 = (float)(blockIdx.y * kTileY);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    bool done = !inside;
+    // Tg is the transmittance the list walk multiplies with: equal to T while the pixel is live, 0 once it has
+    // terminated (or lies outside the image).  A dead pixel then fails the 1e-4 test by itself, so the walk needs
+    // no separate "done" branch; T keeps the value at termination for the output.
+    float Tg = inside ? 1.0f : 0.0f;
 
     const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
     const int rounds = (int)((range.y - range.x + kBatch - 1) / kBatch);
@@ -82,7 +88,7 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
     float C0 = 0.f, C1 = 0.f, C2 = 0.f;
 
     for (int i = 0; i < rounds; ++i, to_do -= kBatch) {
-        if (__syncthreads_count(done) == kTilePixels) break;
+        if (__syncthreads_count(Tg == 0.0f) == kTilePixels) break;
         const uint32_t progress = (uint32_t)i * kBatch + tr;
         if (range.x + progress < range.y) {
             const uint32_t id = __ldg(point_list + range.x + progress);
@@ -91,24 +97,25 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
             const float r = __ldg(features + 3 * (size_t)id);
             const float g = __ldg(features + 3 * (size_t)id + 1);
             const float b = __ldg(features + 3 * (size_t)id + 2);
-            s_a[tr] = make_float4(xy.x, xy.y, co.x, co.y);
-            s_b[tr] = make_float4(co.z, co.w, r, g);
-            s_c[tr] = b;
+            s_rec[3 * tr] = make_float4(xy.x, xy.y, co.x, co.y);
+            s_rec[3 * tr + 1] = make_float4(co.z, co.w, r, g);
+            s_rec[3 * tr + 2].x = b;
             s_mask[tr] = warp_block_mask(xy.x, xy.y, co.x, co.y, co.z, co.w, tile_x0, tile_y0);
         }
         __syncthreads();
 
         const int lim = min(kBatch, to_do);
         for (int j0 = 0; j0 < lim; j0 += 32) {
-            if (__all_sync(0xffffffffu, done)) break;
+            if (__all_sync(0xffffffffu, Tg == 0.0f)) break;
             const bool hit = (j0 + lane < lim) && ((s_mask[j0 + lane] >> warp) & 1u);
             uint32_t bits = __ballot_sync(0xffffffffu, hit);
             while (bits) {
                 const int j = j0 + __ffs(bits) - 1;
                 bits &= bits - 1;
-                if (done) continue;
-                const float4 A = s_a[j];
-                const float4 B = s_b[j];
+                const uint32_t ra = rec_addr + 48u * j;
+                float4 A, B;
+                asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(A.x), "=f"(A.y), "=f"(A.z), "=f"(A.w) : "r"(ra));
+                asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4+16];" : "=f"(B.x), "=f"(B.y), "=f"(B.z), "=f"(B.w) : "r"(ra));
                 // Every product/sum below is pinned (_rn intrinsics are never re-fused by ptxas) to
                 // the FMA placement of the reference build: q = fma(dx, cx*dx, cz*dy*dy),
                 // power = fma(q, -0.5, -(cy*dx*dy)), C = fma(T, alpha*c, C).
@@ -118,15 +125,17 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
                 if (power > 0.0f) continue;
                 const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
                 if (alpha < 1.0f / 255.0f) continue;
-                const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+                const float test_T = __fmul_rn(Tg, __fsub_rn(1.0f, alpha));
                 if (test_T < 0.0001f) {
-                    done = true;
+                    Tg = 0.0f;       // terminated (a dead pixel lands here again and again, harmlessly)
                     continue;
                 }
-                C0 = __fmaf_rn(T, __fmul_rn(alpha, B.z), C0);
-                C1 = __fmaf_rn(T, __fmul_rn(alpha, B.w), C1);
-                C2 = __fmaf_rn(T, __fmul_rn(alpha, s_c[j]), C2);
-                T = test_T;
+                float cb;
+                asm volatile("ld.shared.f32 %0, [%1+32];" : "=f"(cb) : "r"(ra));
+                C0 = __fmaf_rn(Tg, __fmul_rn(alpha, B.z), C0);
+                C1 = __fmaf_rn(Tg, __fmul_rn(alpha, B.w), C1);
+                C2 = __fmaf_rn(Tg, __fmul_rn(alpha, cb), C2);
+                T = Tg = test_T;
                 last_contributor = (uint32_t)(i * kBatch + j + 1);
             }
         }
