@@ -49,6 +49,37 @@ __device__ __forceinline__ float warp_sum(float v)
     return v;
 }
 
+// Sums eight per-lane values over the warp with 9 shuffles instead of 40: every exchange also halves the
+// number of values a lane still carries.  On return lane L holds, in v[0], the warp total of value
+// q = 4 * bit4(L) + 2 * bit3(L) + bit2(L)  (the four lanes sharing L >> 2 hold the same total).
+__device__ __forceinline__ float warp_sum8(float (&v)[8], int lane)
+{
+    {
+        const bool up = lane & 16;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float recv = __shfl_xor_sync(0xffffffffu, up ? v[i] : v[i + 4], 16);
+            v[i] = (up ? v[i + 4] : v[i]) + recv;
+        }
+    }
+    {
+        const bool up = lane & 8;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const float recv = __shfl_xor_sync(0xffffffffu, up ? v[i] : v[i + 2], 8);
+            v[i] = (up ? v[i + 2] : v[i]) + recv;
+        }
+    }
+    {
+        const bool up = lane & 4;
+        const float recv = __shfl_xor_sync(0xffffffffu, up ? v[0] : v[1], 4);
+        v[0] = (up ? v[1] : v[0]) + recv;
+    }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+    return v[0];
+}
+
 __global__ void __launch_bounds__(kTilePixels)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                       const float* __restrict__ bg, const float2* __restrict__ means2D,
@@ -58,10 +89,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       float* __restrict__ dL_dconic /*[P][4]*/, float* __restrict__ dL_dopacity,
                       float* __restrict__ dL_dcolors)
 {
-    __shared__ float4 s_a[kBatch];     // x, y, conic.x, conic.y
-    __shared__ float4 s_b[kBatch];     // conic.z, opacity, r, g
-    __shared__ float s_c[kBatch];      // b
+    __shared__ __align__(16) float4 s_rec[3 * kBatch];   // per instance: {x, y, conic.x, conic.y}, {conic.z, opacity, r, g}, {b, -, -, -}
     __shared__ uint32_t s_mask[kBatch];
+    uint32_t rec_addr;   // pinned 32-bit shared address, see blend.cu
+    asm volatile("mov.u32 %0, %1;" : "=r"(rec_addr) : "r"((uint32_t)__cvta_generic_to_shared(s_rec)));
     __shared__ uint32_t s_id[kBatch];
     __shared__ float s_acc[kBatch][9];  // per staged instance: dcolor[3], dmean2D[2], dconic[3], dopacity
     __shared__ uint32_t s_max;
@@ -105,9 +136,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const float2 xy = __ldg(means2D + id);
             const float4 co = __ldg(conic_opacity + id);
             s_id[tr] = id;
-            s_a[tr] = make_float4(xy.x, xy.y, co.x, co.y);
-            s_b[tr] = make_float4(co.z, co.w, __ldg(colors + 3 * (size_t)id), __ldg(colors + 3 * (size_t)id + 1));
-            s_c[tr] = __ldg(colors + 3 * (size_t)id + 2);
+            s_rec[3 * tr] = make_float4(xy.x, xy.y, co.x, co.y);
+            s_rec[3 * tr + 1] = make_float4(co.z, co.w, __ldg(colors + 3 * (size_t)id), __ldg(colors + 3 * (size_t)id + 1));
+            s_rec[3 * tr + 2].x = __ldg(colors + 3 * (size_t)id + 2);
             s_mask[tr] = warp_block_mask(xy.x, xy.y, co.x, co.y, co.z, co.w, tile_x0, tile_y0);
         }
 #pragma unroll
@@ -125,8 +156,12 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 float g[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                 bool active = k < last_contributor;
                 if (active) {
-                    const float4 A = s_a[j];
-                    const float4 B = s_b[j];
+                    const uint32_t ra = rec_addr + 48u * j;
+                    float4 A, B;
+                    float cb;
+                    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(A.x), "=f"(A.y), "=f"(A.z), "=f"(A.w) : "r"(ra));
+                    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4+16];" : "=f"(B.x), "=f"(B.y), "=f"(B.z), "=f"(B.w) : "r"(ra));
+                    asm volatile("ld.shared.f32 %0, [%1+32];" : "=f"(cb) : "r"(ra));
                     const float dx = A.x - fx, dy = A.y - fy;
                     const float power = -0.5f * (A.z * dx * dx + B.x * dy * dy) - A.w * dx * dy;
                     active = !(power > 0.0f);
@@ -137,7 +172,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                         if (active) {
                             T = T / (1.f - alpha);
                             const float dchannel_dcolor = alpha * T;
-                            const float col[3] = {B.z, B.w, s_c[j]};
+                            const float col[3] = {B.z, B.w, cb};
                             float dL_dalpha = 0.f;
 #pragma unroll
                             for (int ch = 0; ch < 3; ++ch) {
@@ -163,11 +198,12 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     }
                 }
                 if (__any_sync(0xffffffffu, active)) {
-#pragma unroll
-                    for (int q = 0; q < 9; ++q) {
-                        const float v = warp_sum(g[q]);
-                        if (lane == 0) atomicAdd(&s_acc[j][q], v);
-                    }
+                    // g[0..7] through the butterfly (lane L ends up with the total of value q(L)), g[8] the plain way
+                    const float last = warp_sum(g[8]);
+                    float (&g8)[8] = reinterpret_cast<float (&)[8]>(g);
+                    const float tot = warp_sum8(g8, lane);
+                    if ((lane & 3) == 0) atomicAdd(&s_acc[j][((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)], tot);
+                    if (lane == 1) atomicAdd(&s_acc[j][8], last);
                 }
             }
         }
