@@ -3,11 +3,15 @@ namespace ggd {
 namespace {
 
 // shared memory map (bytes)
-constexpr uint32_t kOffX0 = 256, kOffA = kOffX0 + 128 * kK0 * 2, kOffG = kOffA + 128 * kKH * 2,
-                   kOffDY = kOffG + 3 * kWT12, kOffDy32 = kOffDY + kWT3, kOffW = kOffDy32 + 128 * 4 * 4,
-                   kSmemTotal = kOffW + 2 * kSlotBytes;
-enum { BW_FULL = 0, BW_EMPTY = 2, B_ACC = 4, B_READY = 5 };
-constexpr uint32_t kColAcc = 0, kColY = 128, kColDX = 160;     // TMEM columns
+constexpr int kWSlots = 3;   // weight blocks in flight: the loader runs up to three MMA steps ahead
+constexpr uint32_t kOffX0 = 256, kOffA = kOffX0 + 128 * kK0 * 2, kOffDZ = kOffA + 128 * kKH * 2,
+                   kOffDY = kOffDZ + kWT12, kOffDy32 = kOffDY + kWT3, kOffW = kOffDy32 + 128 * 4 * 4,
+                   kSmemTotal = kOffW + kWSlots * kSlotBytes;
+enum { BW_FULL = 0, BW_EMPTY = kWSlots, B_ACC = 2 * kWSlots, B_READY = 2 * kWSlots + 1, B_NBARS = 2 * kWSlots + 2 };
+// TMEM columns: step accumulator | last-layer output | dX_0 (summed over heads) | gelu'(z_l) of the three hidden
+// layers as packed fp16 (64 columns each) | last-layer weight gradients (16 columns per head, summed over tiles)
+constexpr uint32_t kColAcc = 0, kColY = 128, kColDX = 160, kColG = 256;
+__host__ __device__ constexpr uint32_t col_dw3(int hi) { return hi < 4 ? 448u + 16u * (uint32_t)hi : 144u; }
 
 struct StepDesc { uint32_t src_off, bytes; };
 __device__ __forceinline__ StepDesc step_weights(int s)
@@ -41,8 +45,7 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
     const int chain0 = kFeat + L.pos_dim;
 
     if (tid == 0) {
-        for (int i = 0; i < 5; ++i) ptx::mbar_init(&bars[i], 1);
-        ptx::mbar_init(&bars[B_READY], 16);
+        for (int i = 0; i < B_NBARS; ++i) ptx::mbar_init(&bars[i], i == B_READY ? 16 : 1);
         ptx::mbar_fence_init();
     }
     if (warp == 16) ptx::tmem_alloc<512>(tmem_slot);
@@ -129,24 +132,26 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
                 const int gp = p0 + r;
                 // ---- forward recompute: layers 0..2 ----
                 for (int l = 0; l < 3; ++l) {
-                    uint8_t* G = smem + kOffG + l * kWT12;
                     wait_acc();
                     uint32_t v[32];
                     ptx::tmem_ld32(trow + kColAcc + colq * 32, v);
                     ptx::tmem_ld_wait();
+                    uint32_t od[16];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        uint32_t og[4], od[4];
+                        uint32_t og[4];
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             __half2 g, dg;
                             gelu_and_grad_h2(__floats2half2_rn(__uint_as_float(v[8 * j + 2 * q]), __uint_as_float(v[8 * j + 2 * q + 1])), g, dg);
                             og[q] = *reinterpret_cast<const uint32_t*>(&g);
-                            od[q] = *reinterpret_cast<const uint32_t*>(&dg);
+                            od[4 * j + q] = *reinterpret_cast<const uint32_t*>(&dg);
                         }
                         *reinterpret_cast<uint4*>(Abuf + canon(r, colq * 32 + 8 * j, kKH)) = make_uint4(og[0], og[1], og[2], og[3]);
-                        *reinterpret_cast<uint4*>(G + canon(r, colq * 32 + 8 * j, kHidden)) = make_uint4(od[0], od[1], od[2], od[3]);
                     }
+                    // gelu'(z_l) waits in tensor memory for the backward steps (16 packed columns per thread)
+                    tmem_st16(trow + kColG + l * 64 + colq * 16, od);
+                    tmem_st_wait();
                     signal_ready();
                 }
                 // ---- last layer: y -> dL/dy (activation derivative, chained gradient from later heads) ----
@@ -175,38 +180,31 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
                     *reinterpret_cast<float4*>(dy32 + 4 * r) = make_float4(dy[0], dy[1], dy[2], dy[3]);
                 }
                 epi_barrier();
-                // last-layer weight / bias gradient, reduced over the tile: thread = (k = r, j = colq)
-                if (colq < n_out) {
-                    float sacc = 0.f;
-                    for (int p = 0; p < kM; ++p)
-                        sacc = fmaf(dy32[4 * p + colq], __half2float(*reinterpret_cast<const __half*>(Abuf + canon(p, r, kKH))), sacc);
-                    atomicAdd(a.dflat + L.flat_w[h][3] + (size_t)colq * kHidden + r, sacc);
-                    if (r == 0) {
-                        float sb = 0.f;
-                        for (int p = 0; p < kM; ++p) sb += dy32[4 * p + colq];
-                        atomicAdd(a.dflat + L.flat_b[h][3] + colq, sb);
-                    }
+                // last-layer bias gradient, reduced over the tile (the weight gradient is an MMA issued with the next
+                // step: dW3 += H3^T dY into its own TMEM accumulator, flushed once at the end of the kernel)
+                if (colq < n_out && r == 0) {
+                    float sb = 0.f;
+                    for (int p = 0; p < kM; ++p) sb += dy32[4 * p + colq];
+                    atomicAdd(a.dflat + L.flat_b[h][3] + colq, sb);
                 }
                 signal_ready();
                 // ---- backward: dZ_l = (dZ_{l+1} W_{l+1}) * G_l for l = 2, 1, 0 (in place over G_l) ----
                 for (int l = 2; l >= 0; --l) {
-                    uint8_t* G = smem + kOffG + l * kWT12;
                     wait_acc();
-                    uint32_t v[32];
+                    uint32_t v[32], gw[16];
                     ptx::tmem_ld32(trow + kColAcc + colq * 32, v);
+                    tmem_ld16(trow + kColG + l * 64 + colq * 16, gw);
                     ptx::tmem_ld_wait();
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        uint4* gp4 = reinterpret_cast<uint4*>(G + canon(r, colq * 32 + 8 * j, kHidden));
-                        uint4 gv = *gp4;
-                        uint32_t* gw = reinterpret_cast<uint32_t*>(&gv);
+                        uint32_t oz[4];
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const __half2 dh = __floats2half2_rn(__uint_as_float(v[8 * j + 2 * q]), __uint_as_float(v[8 * j + 2 * q + 1]));
-                            const __half2 dz = __hmul2(dh, *reinterpret_cast<const __half2*>(&gw[q]));
-                            gw[q] = *reinterpret_cast<const uint32_t*>(&dz);
+                            const __half2 dz = __hmul2(dh, *reinterpret_cast<const __half2*>(&gw[4 * j + q]));
+                            oz[q] = *reinterpret_cast<const uint32_t*>(&dz);
                         }
-                        *gp4 = gv;
+                        *reinterpret_cast<uint4*>(smem + kOffDZ + canon(r, colq * 32 + 8 * j, kHidden)) = make_uint4(oz[0], oz[1], oz[2], oz[3]);
                     }
                     signal_ready();
                 }
@@ -239,6 +237,16 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
                         }
                     }
                 }
+            }
+        }
+        // ---- last-layer weight gradients: lane = input unit, 16 columns per head ----
+        if (colq == 0) {
+            for (int hi = 0; hi < kHeads; ++hi) {
+                const int h = L.order[hi], n_out = head_out(h);
+                uint32_t wv[4];
+                ptx::tmem_ld4(trow + col_dw3(hi), wv);
+                ptx::tmem_ld_wait();
+                for (int j = 0; j < n_out; ++j) atomicAdd(a.dflat + L.flat_w[h][3] + (size_t)j * kHidden + r, __uint_as_float(wv[j]));
             }
         }
     }

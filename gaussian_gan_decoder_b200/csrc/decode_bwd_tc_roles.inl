@@ -4,6 +4,7 @@
         if (lane == 0) {
             const uint32_t sb = ptx::smem_u32(smem);
             const uint32_t id128 = ptx::idesc_f16(kM, 128), id16 = ptx::idesc_f16(kM, 16), id48 = ptx::idesc_f16(kM, kK0);
+            const uint32_t id_dw3 = ptx::idesc_f16(128, 16) | (1u << 15) | (1u << 16);   // both operands MN-major (K = points)
             uint32_t cnt = 0, n_ready = 0;
             auto mma_k = [&](uint32_t d, uint32_t a_addr, uint32_t a_K, uint32_t b_addr, uint32_t b_K, uint32_t idesc, int ksteps, bool acc0) {
                 for (int s = 0; s < ksteps; ++s)
@@ -14,26 +15,33 @@
                 for (int hi = kHeads - 1; hi >= 0; --hi) {
                     const int h = L.order[hi];
                     for (int s = 0; s < 8; ++s, ++cnt) {
-                        const uint32_t slot = cnt & 1;
+                        const uint32_t slot = cnt % kWSlots;
                         const uint32_t w_addr = sb + kOffW + slot * kSlotBytes;
-                        ptx::mbar_wait(&bars[BW_FULL + slot], (cnt >> 1) & 1);
+                        ptx::mbar_wait(&bars[BW_FULL + slot], (cnt / kWSlots) & 1);
                         ptx::mbar_wait(&bars[B_READY], n_ready & 1);
                         ++n_ready;
                         ptx::tc_fence_after();
                         bool stored = false;
                         if (s == 0 && hi == kHeads - 1) { bulk_s2g(a.stage + st.x0_off + (size_t)tile * st.x0_tile, smem + kOffX0, (uint32_t)st.x0_tile); stored = true; }
                         if (s == 1 || s == 2) { bulk_s2g(a.stage + st.h_off[h][s - 1] + (size_t)tile * st.h_tile, smem + kOffA, (uint32_t)st.h_tile); stored = true; }
-                        if (s >= 5) { const int l = 7 - s; bulk_s2g(a.stage + st.dz_off[h][l] + (size_t)tile * st.dz_tile, smem + kOffG + l * kWT12, (uint32_t)st.dz_tile); stored = true; }
+                        if (s >= 5) { const int l = 7 - s; bulk_s2g(a.stage + st.dz_off[h][l] + (size_t)tile * st.dz_tile, smem + kOffDZ, (uint32_t)st.dz_tile); stored = true; }
                         if (stored) bulk_commit();
                         const uint32_t dacc = tmem_base + kColAcc;
                         switch (s) {
                             case 0: mma_k(dacc, sb + kOffX0, kK0, w_addr, kK0, id128, kK0 / 16, false); break;
                             case 1: case 2: mma_k(dacc, sb + kOffA, kKH, w_addr, kKH, id128, kKH / 16, false); break;
                             case 3: mma_k(tmem_base + kColY, sb + kOffA, kKH, w_addr, kKH, id16, kKH / 16, false); break;
-                            case 4: mma_k(dacc, sb + kOffDY, 16, w_addr, 16, id128, 1, false); break;
-                            case 5: mma_k(dacc, sb + kOffG + 2 * kWT12, kHidden, w_addr, kHidden, id128, kHidden / 16, false); break;
-                            case 6: mma_k(dacc, sb + kOffG + 1 * kWT12, kHidden, w_addr, kHidden, id128, kHidden / 16, false); break;
-                            default: mma_k(tmem_base + kColDX, sb + kOffG, kHidden, w_addr, kHidden, id48, kHidden / 16, hi != kHeads - 1); break;
+                            case 4:
+                                mma_k(dacc, sb + kOffDY, 16, w_addr, 16, id128, 1, false);
+                                // dW3[k][j] += sum over the tile's points H3[p][k] dY[p][j]: H3 is still in the hidden operand
+                                // buffer ([point][unit], 144 columns), dY is [point][16]; contraction over the strided index
+                                for (int s2 = 0; s2 < kM / 16; ++s2)
+                                    ptx::mma_f16_ss(tmem_base + col_dw3(hi), ptx::smem_desc(sb + kOffA + s2 * 2 * (kKH * 16), kKH * 16, 128),
+                                                    ptx::smem_desc(sb + kOffDY + s2 * 2 * 256, 256, 128), id_dw3,
+                                                    (tile != (int)blockIdx.x || s2 > 0) ? 1u : 0u);
+                                break;
+                            case 5: case 6: mma_k(dacc, sb + kOffDZ, kHidden, w_addr, kHidden, id128, kHidden / 16, false); break;
+                            default: mma_k(tmem_base + kColDX, sb + kOffDZ, kHidden, w_addr, kHidden, id48, kHidden / 16, hi != kHeads - 1); break;
                         }
                         if (stored) bulk_wait_read();
                         ptx::mma_commit(&bars[B_ACC]);
@@ -51,8 +59,8 @@
                 for (int hi = kHeads - 1; hi >= 0; --hi) {
                     const int h = L.order[hi];
                     for (int s = 0; s < 8; ++s, ++cnt) {
-                        const uint32_t slot = cnt & 1;
-                        if (cnt >= 2) ptx::mbar_wait(&bars[BW_EMPTY + slot], ((cnt >> 1) - 1) & 1);
+                        const uint32_t slot = cnt % kWSlots;
+                        if (cnt >= (uint32_t)kWSlots) ptx::mbar_wait(&bars[BW_EMPTY + slot], ((cnt / kWSlots) - 1) & 1);
                         const StepDesc d = step_weights(s);
                         const uint8_t* src = s < 4 ? args.packed_fwd + (size_t)h * kFwdPackHead + d.src_off
                                                    : args.packed_bwd + (size_t)h * kBwdPackHead + d.src_off;
