@@ -4,11 +4,12 @@
 // sampled features and to the chained inputs — but every dense contraction is an MMA:
 //   forward   z_l  = H_l  W_l^T          (4 MMAs per head, weights from the forward fp16 pack)
 //   backward  dH_l = dZ_l W_l            (4 MMAs per head, weights from a transposed fp16 pack)
-// The epilogue warps turn z_l into H_{l+1} = gelu(z_l) and G_l = gelu'(z_l) (kept in shared
-// memory), and dH_l into dZ_{l-1} = dH_l * G_{l-1} (written over G_{l-1}).  H_l and dZ_l tiles
-// are streamed to the staging area with bulk async stores; decode_bwd_dw_mn.cu turns them into
-// weight gradients.  The feature / chained-input gradient dX_0 accumulates ACROSS heads in a
-// dedicated TMEM accumulator, so the chain rule between heads costs nothing.
+// The epilogue warps turn z_l into H_{l+1} = gelu(z_l) and G_l = gelu'(z_l) (kept in tensor memory as
+// packed fp16, written with tcgen05.st), and dH_l into dZ_{l-1} = dH_l * G_{l-1}.  H_l and dZ_l tiles
+// are streamed to the staging area with bulk async stores; decode_bwd_dw_mn.cu turns them into the
+// hidden layers' weight gradients.  The feature / chained-input gradient dX_0 accumulates ACROSS heads in
+// a dedicated TMEM accumulator, so the chain rule between heads costs nothing; the last layers' weight
+// gradients accumulate ACROSS tiles in five more (dW3 += H_3^T dY, both operands MN-major).
 // Replaces the same autograd graph as decode_bwd.cu (see there for reference citations).
 #include "decode_bwd.cuh"
 #include "decode_args.cuh"
