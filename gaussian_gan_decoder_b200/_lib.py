@@ -51,6 +51,8 @@ SIGNATURES = {
     "ggd_raster_backward": (_i, [_p, _i, _i, _i, _p, _i, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                                  _p, _p, _u64, _p] + [_p] * 10),
     "ggd_raster_status": (_i, [_p, _p, _i, C.POINTER(C.c_uint32)]),
+    "ggd_surface_points_scratch_bytes": (C.c_size_t, [_i]),
+    "ggd_surface_points": (_i, [_p, _p, _i, C.c_float, C.c_uint64, _i, C.c_float, _p, C.c_size_t, _p, _p]),
     "ggd_raster_binning": (_i, [_i]),
     "ggd_raster_binning_info": (_i, [_p, _p, _i, C.POINTER(C.c_uint32)]),
     "ggd_mark_visible": (_i, [_p, _i, _p, _p, _p, _p]),

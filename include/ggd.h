@@ -306,6 +306,23 @@ GGD_API int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, con
                                 const float* dL_dopacity, const float* dL_dcolor,
                                 void* scratch, size_t scratch_bytes, float* dflat, float* dplanes);
 
+/* ---- point-set producer -------------------------------------------------
+ * Iso-surface points of a density grid, on the GPU.  Replaces the CPU detour of
+ * main/decoder_utils/target_dataloader.py:96-118 + :185-190 (skimage.measure.marching_cubes on the
+ * 128^3 sigma grid, trimesh, one random barycentric point per face repeated until n_points exist,
+ * truncation, radial scale clip(randn * thickness + 1, 0, 1)).  sigma is [res][res][res] fp32 in the
+ * reference's index order; a mesh vertex at index coordinates v maps to v / res - 0.5.  The cells are
+ * tessellated with six tetrahedra each (no case tables), point k lies on triangle k mod n_triangles,
+ * random numbers are counter-based from `seed`: results are reproducible and match
+ * oracle/surface_oracle.py; against the reference the agreement is statistical (different
+ * triangulation and random stream).  scratch: ggd_surface_points_scratch_bytes(res), 256-byte
+ * aligned.  num_triangles_host (optional, pinned) receives the triangle count asynchronously;
+ * with no triangle at all the points are zeros.  points may be null when n_points is 0. */
+GGD_API size_t ggd_surface_points_scratch_bytes(int res);
+GGD_API int ggd_surface_points(void* stream, const float* sigma, int res, float level, uint64_t seed, int n_points,
+                               float thickness, void* scratch, size_t scratch_bytes, float* points,
+                               uint32_t* num_triangles_host);
+
 #ifdef __cplusplus
 }
 #endif
