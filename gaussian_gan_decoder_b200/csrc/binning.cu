@@ -20,6 +20,7 @@
 //  * the element count lives in device memory; grids are sized by the buffer
 //    capacity and surplus CTAs exit, so no host round-trip is needed.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace ggd {
 
@@ -164,7 +165,11 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp
     return off + incl - v;
 }
 
-__global__ void __launch_bounds__(kSortThreads)
+// kMinCtas: resident CTAs per SM the register allocation aims at.  2 -> 128 registers, no spills: fastest when a pass
+// is a few hundred CTAs and latency-bound (the headline frame); 4 -> 64 registers with some spilled words, but
+// twice the warps in flight: fastest when a pass streams tens of MB or more (trained-like and 2048^2 frames).
+template <int kMinCtas>
+__global__ void __launch_bounds__(kSortThreads, kMinCtas)
 onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
                 const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                 const uint32_t* __restrict__ n_ptr, uint32_t capacity, int shift, uint32_t mask,
@@ -391,9 +396,13 @@ int sort_pairs(cudaStream_t s, const uint64_t* keys_in, uint64_t* keys_out, cons
         const uint32_t* vin = (p == 0) ? vals_in : (to_out ? vals_tmp : vals_out);
         uint64_t* kout = to_out ? keys_out : keys_tmp;
         uint32_t* vout = to_out ? vals_out : vals_tmp;
-        onesweep_kernel<<<tiles, kSortThreads, 0, s>>>(kin, kout, vin, vout, n_dev, cap, shift, mask,
-                                                       sc.hist + p * kRadixBins,
-                                                       sc.lookback + p * lb_stride, sc.tickets + p);
+        // measured on B200: R = 0.8 M -> 0.117 ms (2 CTAs/SM) vs 0.148 (4); R = 6.5 M -> 0.58 vs 0.44; R = 280 M -> 21 vs 13.5 ms
+        if (capacity >= (4ull << 20))
+            onesweep_kernel<4><<<tiles, kSortThreads, 0, s>>>(kin, kout, vin, vout, n_dev, cap, shift, mask, sc.hist + p * kRadixBins,
+                                                              sc.lookback + p * lb_stride, sc.tickets + p);
+        else
+            onesweep_kernel<2><<<tiles, kSortThreads, 0, s>>>(kin, kout, vin, vout, n_dev, cap, shift, mask, sc.hist + p * kRadixBins,
+                                                              sc.lookback + p * lb_stride, sc.tickets + p);
         GGD_LAUNCH_CHECK("onesweep_kernel");
     }
     return GGD_OK;
