@@ -165,16 +165,29 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp
     return off + incl - v;
 }
 
+// One CTA: bit q of *plan = pass q's digit is the same for all n keys.
+__global__ void __launch_bounds__(kRadixBins)
+sort_plan_kernel(const uint32_t* __restrict__ hist, const uint32_t* __restrict__ n_ptr, uint32_t capacity, int num_passes,
+                 uint32_t* __restrict__ plan)
+{
+    const uint32_t n = min(__ldg(n_ptr), capacity);
+    uint32_t m = 0;
+    for (int q = 0; q < num_passes; ++q)
+        if (__syncthreads_or(n != 0 && hist[q * kRadixBins + threadIdx.x] == n)) m |= 1u << q;
+    if (threadIdx.x == 0) *plan = m;
+}
+
 // kMinCtas: resident CTAs per SM the register allocation aims at.  2 -> 128 registers, no spills: fastest when a pass
 // is a few hundred CTAs and latency-bound (the headline frame); 4 -> 64 registers with some spilled words, but
 // twice the warps in flight: fastest when a pass streams tens of MB or more (trained-like and 2048^2 frames).
 template <int kMinCtas>
 __global__ void __launch_bounds__(kSortThreads, kMinCtas)
-onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
-                const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
+onesweep_kernel(const uint64_t* __restrict__ keys_src, uint64_t* __restrict__ keys_a, uint64_t* __restrict__ keys_b,
+                const uint32_t* __restrict__ vals_src, uint32_t* __restrict__ vals_a, uint32_t* __restrict__ vals_b,
                 const uint32_t* __restrict__ n_ptr, uint32_t capacity, int shift, uint32_t mask,
                 const uint32_t* __restrict__ hist /*[256] digit counts of this pass*/,
-                uint32_t* __restrict__ lookback /*[tiles][256]*/, uint32_t* __restrict__ ticket)
+                uint32_t* __restrict__ lookback /*[tiles][256]*/, uint32_t* __restrict__ ticket,
+                const uint32_t* __restrict__ plan /*bit q: pass q is the identity*/, int pass, int num_passes)
 {
     __shared__ __align__(16) uint64_t s_keys[kSortTile];       // 32 KB, reused for values
     __shared__ uint32_t s_whist[kSortWarps][kRadixBins];        // 8 KB
@@ -194,19 +207,33 @@ onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ key
     if (tile_base >= n) return;
     const uint32_t n_valid = (uint32_t)min((uint64_t)kSortTile, (uint64_t)n - tile_base);
 
-    // ---- trivial digit: if one bin holds every key (e.g. the exponent byte of depths that all lie
-    // in [2,4), or tile-id bits above the tile count) the pass is the identity permutation: copy
-    // the tile to the other buffer and skip ranking, look-back and scatter.
-    if (__syncthreads_or(__ldg(hist + t) == n)) {
+    // ---- which buffers this pass works on.  A pass whose digit is the same for every key (the exponent byte of
+    // depths that all lie in [2,4), tile-id bits above the tile count) is the identity permutation and is skipped
+    // outright; sort_plan_kernel found those from the histograms.  The remaining passes ping-pong between the two
+    // buffer sets such that the LAST of them lands in set a (the caller's output): counted from the back.
+    const uint32_t ident = __ldg(plan);
+    const int real_total = num_passes - __popc(ident & ((1u << num_passes) - 1u));
+    const uint64_t* keys_in; const uint32_t* vals_in;
+    uint64_t* keys_out; uint32_t* vals_out;
+    if ((ident >> pass) & 1u) {
+        if (real_total != 0 || pass != num_passes - 1) return;
+        // every pass is the identity (one key, or all keys equal in the sorted bits): the output is the input
 #pragma unroll
         for (int k = 0; k < kSortItems; ++k) {
             const uint32_t li = t + k * kSortThreads;
             if (li < n_valid) {
-                keys_out[tile_base + li] = __ldg(keys_in + tile_base + li);
-                vals_out[tile_base + li] = __ldg(vals_in + tile_base + li);
+                keys_a[tile_base + li] = __ldg(keys_src + tile_base + li);
+                vals_a[tile_base + li] = __ldg(vals_src + tile_base + li);
             }
         }
         return;
+    }
+    {
+        const int j = __popc(~ident & ((1u << pass) - 1u));          // real passes before this one
+        const bool to_a = ((real_total - 1 - j) & 1) == 0;
+        keys_out = to_a ? keys_a : keys_b; vals_out = to_a ? vals_a : vals_b;
+        keys_in = j == 0 ? keys_src : (to_a ? keys_b : keys_a);
+        vals_in = j == 0 ? vals_src : (to_a ? vals_b : vals_a);
     }
 
     // ---- load (warp-striped: item k of lane l sits at warp_base + k*32 + l)
@@ -386,23 +413,22 @@ int sort_pairs(cudaStream_t s, const uint64_t* keys_in, uint64_t* keys_out, cons
         GGD_LAUNCH_CHECK("histogram_kernel");
     }
     const size_t lb_stride = (size_t)(tiles + 1) * kRadixBins;
+    uint32_t* plan = sc.tickets + 16;
+    sort_plan_kernel<<<1, kRadixBins, 0, s>>>(sc.hist, n_dev, cap, num_passes, plan);
+    GGD_LAUNCH_CHECK("sort_plan_kernel");
     for (int p = 0; p < num_passes; ++p) {
         const int shift = begin_bit + p * kRadixBits;
         const int bits = std::min(kRadixBits, end_bit - shift);
         const uint32_t mask = (1u << bits) - 1u;
-        // the last pass lands in *_out; passes alternate backwards from there
-        const bool to_out = ((num_passes - 1 - p) % 2) == 0;
-        const uint64_t* kin = (p == 0) ? keys_in : (to_out ? keys_tmp : keys_out);
-        const uint32_t* vin = (p == 0) ? vals_in : (to_out ? vals_tmp : vals_out);
-        uint64_t* kout = to_out ? keys_out : keys_tmp;
-        uint32_t* vout = to_out ? vals_out : vals_tmp;
         // measured on B200: R = 0.8 M -> 0.117 ms (2 CTAs/SM) vs 0.148 (4); R = 6.5 M -> 0.58 vs 0.44; R = 280 M -> 21 vs 13.5 ms
         if (capacity >= (4ull << 20))
-            onesweep_kernel<4><<<tiles, kSortThreads, 0, s>>>(kin, kout, vin, vout, n_dev, cap, shift, mask, sc.hist + p * kRadixBins,
-                                                              sc.lookback + p * lb_stride, sc.tickets + p);
+            onesweep_kernel<4><<<tiles, kSortThreads, 0, s>>>(keys_in, keys_out, keys_tmp, vals_in, vals_out, vals_tmp, n_dev, cap, shift,
+                                                              mask, sc.hist + p * kRadixBins, sc.lookback + p * lb_stride,
+                                                              sc.tickets + p, plan, p, num_passes);
         else
-            onesweep_kernel<2><<<tiles, kSortThreads, 0, s>>>(kin, kout, vin, vout, n_dev, cap, shift, mask, sc.hist + p * kRadixBins,
-                                                              sc.lookback + p * lb_stride, sc.tickets + p);
+            onesweep_kernel<2><<<tiles, kSortThreads, 0, s>>>(keys_in, keys_out, keys_tmp, vals_in, vals_out, vals_tmp, n_dev, cap, shift,
+                                                              mask, sc.hist + p * kRadixBins, sc.lookback + p * lb_stride,
+                                                              sc.tickets + p, plan, p, num_passes);
         GGD_LAUNCH_CHECK("onesweep_kernel");
     }
     return GGD_OK;

@@ -54,7 +54,7 @@ constexpr int kMaxSortPasses = 8;                     // 64 key bits / 8
 // Scratch layout of one sort: [pass histograms][tile tickets][look-back words]
 struct SortScratch {
     uint32_t* hist;      // [kMaxSortPasses][kRadixBins] digit counts, then exclusive offsets
-    uint32_t* tickets;   // [kMaxSortPasses + 1] dynamic tile ids (last one: histogram kernel)
+    uint32_t* tickets;   // [kMaxSortPasses + 1] dynamic tile ids (last one: histogram kernel); word 16: identity-pass mask
     uint32_t* lookback;  // [kMaxSortPasses][tiles][kRadixBins] decoupled look-back words
     size_t bytes;        // total
     size_t zero_bytes;   // prefix that must be zero before a sort starts
