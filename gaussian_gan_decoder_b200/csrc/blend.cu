@@ -15,6 +15,8 @@
 // 8x4 pixel block and only walks the instances whose conservative footprint
 // touches that block (see warp_block_mask).
 #include "common.cuh"
+#include <algorithm>
+#include <cstdlib>
 
 namespace ggd {
 namespace {
@@ -55,8 +57,9 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
              const float2* __restrict__ means2D, const float* __restrict__ features,
              const float4* __restrict__ conic_opacity, float* __restrict__ final_T,
              uint32_t* __restrict__ n_contrib, const float* __restrict__ bg,
-             float* __restrict__ out_color)
+             float* __restrict__ out_color, uint32_t* __restrict__ work /*[2]: next tile, finished CTAs*/, uint32_t num_tiles)
 {
+    __shared__ uint32_t s_tile_id;
     __shared__ __align__(16) float4 s_rec[3 * kBatch];  // per instance: {x, y, conic.x, conic.y}, {conic.z, opacity, r, g}, {b, -, -, -}
     __shared__ uint32_t s_mask[kBatch];
     // 32-bit shared-window addresses, formed once: inside the list walk the compiler would otherwise rebuild the
@@ -67,19 +70,29 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
 
     const uint32_t tiles_x = (W + kTileX - 1) / kTileX;
     const int tr = threadIdx.x, warp = tr >> 5, lane = tr & 31;
+    // The grid is a few CTAs per SM that pull tiles from a counter until none is left: tile lists differ in length
+    // by more than 10x inside one image, and with one CTA per tile (all resident at once on a 512^2 image) the SMs
+    // that drew long lists finish long after the others.
+    for (;;) {
+    __syncthreads();                      // previous tile's shared records are no longer read
+    if (tr == 0) s_tile_id = atomicAdd(work, 1u);
+    __syncthreads();
+    const uint32_t tile_id = s_tile_id;
+    if (tile_id >= num_tiles) break;
+    const uint32_t tile_bx = tile_id % tiles_x, tile_by = tile_id / tiles_x;
     // warp w owns the 8x4 pixel block at (8*(w&1), 4*(w>>1)) of the tile
-    const uint32_t px = blockIdx.x * kTileX + (warp & 1) * 8 + (lane & 7);
-    const uint32_t py = blockIdx.y * kTileY + (warp >> 1) * 4 + (lane >> 3);
+    const uint32_t px = tile_bx * kTileX + (warp & 1) * 8 + (lane & 7);
+    const uint32_t py = tile_by * kTileY + (warp >> 1) * 4 + (lane >> 3);
     const uint32_t pix_id = W * py + px;
     const float fx = (float)px, fy = (float)py;
-    const float tile_x0 = (float)(blockIdx.x * kTileX), tile_y0 = (float)(blockIdx.y * kTileY);
+    const float tile_x0 = (float)(tile_bx * kTileX), tile_y0 = (float)(tile_by * kTileY);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     // Tg is the transmittance the list walk multiplies with: equal to T while the pixel is live, 0 once it has
     // terminated (or lies outside the image).  A dead pixel then fails the 1e-4 test by itself, so the walk needs
     // no separate "done" branch; T keeps the value at termination for the output.
     float Tg = inside ? 1.0f : 0.0f;
 
-    const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
+    const uint2 range = ranges[tile_id];
     const int rounds = (int)((range.y - range.x + kBatch - 1) / kBatch);
     int to_do = (int)(range.y - range.x);
 
@@ -149,6 +162,9 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
         out_color[plane + pix_id] = __fmaf_rn(T, bg[1], C1);
         out_color[2 * plane + pix_id] = __fmaf_rn(T, bg[2], C2);
     }
+    }   // tile loop
+    // the last CTA out leaves the counters at zero for the next frame
+    if (tr == 0 && atomicAdd(work + 1, 1u) == gridDim.x - 1) { work[0] = 0; work[1] = 0; }
 }
 
 }  // namespace
@@ -157,10 +173,15 @@ int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const Geo
                  const BinState& b, const ImgState& im, const float* features,
                  const float* background, float* out_color)
 {
-    dim3 grid(grid_x, grid_y, 1), block(kTilePixels, 1, 1);
-    blend_kernel<<<grid, block, 0, s>>>(im.ranges, b.vals, W, H, g.means2D, features,
-                                        g.conic_opacity, im.accum_alpha, im.n_contrib, background,
-                                        out_color);
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const char* e = getenv("GGD_BLEND_CTAS");
+    const int per_sm = e ? atoi(e) : 6;
+    const int tiles = grid_x * grid_y;
+    const int grid = std::min(tiles, sms * per_sm);
+    blend_kernel<<<grid, kTilePixels, 0, s>>>(im.ranges, b.vals, W, H, g.means2D, features,
+                                              g.conic_opacity, im.accum_alpha, im.n_contrib, background,
+                                              out_color, g.counters + 8, (uint32_t)tiles);
     GGD_LAUNCH_CHECK("blend_kernel");
     return GGD_OK;
 }
