@@ -87,8 +87,10 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                       const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D /*[P][3]*/,
                       float* __restrict__ dL_dconic /*[P][4]*/, float* __restrict__ dL_dopacity,
-                      float* __restrict__ dL_dcolors)
+                      float* __restrict__ dL_dcolors, uint32_t* __restrict__ work /*[2]: next tile, finished CTAs*/,
+                      uint32_t num_tiles)
 {
+    __shared__ uint32_t s_tile_id;
     __shared__ __align__(16) float4 s_rec[3 * kBatch];   // per instance: {x, y, conic.x, conic.y}, {conic.z, opacity, r, g}, {b, -, -, -}
     __shared__ uint32_t s_mask[kBatch];
     uint32_t rec_addr;   // pinned 32-bit shared address, see blend.cu
@@ -99,13 +101,21 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
     const uint32_t tiles_x = (W + kTileX - 1) / kTileX;
     const int tr = threadIdx.x, warp = tr >> 5, lane = tr & 31;
-    const uint32_t px = blockIdx.x * kTileX + (warp & 1) * 8 + (lane & 7);
-    const uint32_t py = blockIdx.y * kTileY + (warp >> 1) * 4 + (lane >> 3);
+    // persistent CTAs pull tiles from a counter (see blend.cu: tile lists differ a lot in length)
+    for (;;) {
+    __syncthreads();
+    if (tr == 0) s_tile_id = atomicAdd(work, 1u);
+    __syncthreads();
+    const uint32_t tile_id = s_tile_id;
+    if (tile_id >= num_tiles) break;
+    const uint32_t tile_bx = tile_id % tiles_x, tile_by = tile_id / tiles_x;
+    const uint32_t px = tile_bx * kTileX + (warp & 1) * 8 + (lane & 7);
+    const uint32_t py = tile_by * kTileY + (warp >> 1) * 4 + (lane >> 3);
     const uint32_t pix_id = W * py + px;
     const float fx = (float)px, fy = (float)py;
-    const float tile_x0 = (float)(blockIdx.x * kTileX), tile_y0 = (float)(blockIdx.y * kTileY);
+    const float tile_x0 = (float)(tile_bx * kTileX), tile_y0 = (float)(tile_by * kTileY);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
+    const uint2 range = ranges[tile_id];
 
     const float T_final = inside ? final_Ts[pix_id] : 0.f;
     const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
@@ -225,6 +235,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             }
         }
     }
+    }   // tile loop
+    if (tr == 0 && atomicAdd(work + 1, 1u) == gridDim.x - 1) { work[0] = 0; work[1] = 0; }   // leave the queue reset
 }
 
 }  // namespace

@@ -230,9 +230,14 @@ extern "C" int ggd_raster_backward(void* stream, int P, int D, int M, const floa
     if (!radii) radii = g.radii;
     const int grid_x = (W + kTileX - 1) / kTileX, grid_y = (H + kTileY - 1) / kTileY;
     const float* colors = colors_precomp ? colors_precomp : g.rgb;
-    blend_backward_kernel<<<dim3(grid_x, grid_y), kTilePixels, 0, s>>>(
+    // the state buffers are inputs here except for two words of the geometry state's counter block, which serve as the
+    // (self-resetting) tile queue of the persistent kernel
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const int tiles = grid_x * grid_y;
+    blend_backward_kernel<<<tiles < 4 * sms ? tiles : 4 * sms, kTilePixels, 0, s>>>(
         im.ranges, b.vals, W, H, background, g.means2D, g.conic_opacity, colors, im.accum_alpha, im.n_contrib,
-        dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+        dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, g.counters + 10, (uint32_t)tiles);
     GGD_LAUNCH_CHECK("blend_backward_kernel");
     GeomBwdArgs a;
     a.P = P; a.D = D; a.M = shs ? M : 0;
