@@ -1,14 +1,15 @@
 // Stage 2b of the rasteriser: per-tile front-to-back alpha blending.
 //
 // Replaces FORWARD::render → renderCUDA (DGR/cuda_rasterizer/forward.cu:261-400).
-// One CTA per 16x16 tile, one thread per pixel.  The per-pixel arithmetic —
+// A CTA works on one 16x16 tile at a time, one thread per pixel; six persistent CTAs per SM pull
+// tiles from a queue (the reference launches one CTA per tile).  The per-pixel arithmetic —
 // the falloff exponent, alpha = min(0.99, o·exp(power)), the 1/255 and 1e-4
 // tests, C += c·alpha·T, and the contributor bookkeeping — keeps the
 // reference's operation order exactly, because n_contrib (an integer output)
 // and the final T depend on every rounding along the way.
 //
 // What differs: a batch stages, per instance, the complete blend record
-// {xy, conic, opacity, rgb} in shared memory as two float4 + one float, so the
+// {xy, conic, opacity, rgb} in shared memory as a 48-byte record, so the
 // inner loop has no global loads at all (the reference gathers the colour from
 // global memory for every contributing (pixel, Gaussian) pair, forward.cu:355)
 // and every shared-memory read is a 16-byte broadcast; and each warp owns an
