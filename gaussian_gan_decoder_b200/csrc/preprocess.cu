@@ -361,26 +361,36 @@ scan_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
     }
     const uint32_t thread_excl = warp_off + incl - tsum;
 
-    if (threadIdx.x == 0) {
+    if (warp == 0) {
+        // decoupled look-back, 32 predecessors per step: lane i inspects tile (look - i); everything up to the nearest
+        // tile that already knows its inclusive prefix must at least have published its aggregate
         uint32_t excl = 0;
-        if (tile == 0) {
-            atomicExch(reinterpret_cast<unsigned long long*>(&status[0]), kFlagPre | block_sum);
-        } else {
-            atomicExch(reinterpret_cast<unsigned long long*>(&status[tile]), kFlagAgg | block_sum);
+        if (lane == 0)
+            atomicExch(reinterpret_cast<unsigned long long*>(&status[tile]), (tile == 0 ? (2ull << 62) : (1ull << 62)) | block_sum);
+        if (tile != 0) {
             int look = (int)tile - 1;
             while (true) {
-                const uint64_t w = *reinterpret_cast<volatile uint64_t*>(&status[look]);
-                const uint64_t f = w >> 62;
-                if (f == 0) continue;
-                excl += (uint32_t)w;
-                if (f == 2) break;
-                --look;
+                const int idx = look - lane;
+                const uint64_t w = idx >= 0 ? *reinterpret_cast<volatile uint64_t*>(&status[idx]) : (2ull << 62);   // before tile 0: prefix 0
+                const uint32_t f = (uint32_t)(w >> 62);
+                const uint32_t pre = __ballot_sync(0xffffffffu, f == 2), empty = __ballot_sync(0xffffffffu, f == 0);
+                const int first_pre = pre ? __ffs(pre) - 1 : 32;
+                const uint32_t need = first_pre >= 31 ? 0xffffffffu : ((2u << first_pre) - 1u);
+                if (empty & need) continue;                       // a tile in the window has published nothing yet
+                uint32_t part = (lane <= first_pre) ? (uint32_t)w : 0u;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+                excl += part;
+                if (first_pre < 32) break;
+                look -= 32;
             }
-            atomicExch(reinterpret_cast<unsigned long long*>(&status[tile]),
-                       kFlagPre | (uint64_t)(excl + block_sum));
+            if (lane == 0)
+                atomicExch(reinterpret_cast<unsigned long long*>(&status[tile]), kFlagPre | (uint64_t)(excl + block_sum));
         }
-        s_prefix = excl;
-        if (base + kScanTile >= P) counters[0] = excl + block_sum;  // last tile: R
+        if (lane == 0) {
+            s_prefix = excl;
+            if (base + kScanTile >= P) counters[0] = excl + block_sum;  // last tile: R
+        }
     }
     __syncthreads();
     const uint32_t add = s_prefix + thread_excl;
