@@ -82,3 +82,34 @@ def test_packed_planes_handshake(cuda):
     xyz_g = xyz.clone().requires_grad_(False)
     with pytest.raises(RuntimeError):
         dec(z, c, xyz_g, 1.0)                                    # parameters require grad and grad mode is on
+
+
+def test_pipeline_recovers_when_a_frame_stops_qualifying(cuda):
+    """The pipeline promotes itself to tiles-only binning after a qualifying frame.  When a later frame needs more
+    (here: splats blown up so that tile lists and the instance count explode) check() reports `redo`, falls back, and
+    the re-run gives the image of the reference-facing path."""
+    from gaussian_gan_decoder_b200 import rasterizer as rz
+    g = synthetic.gen(10)
+    planes = synthetic.planes("panohead", g, res=64, depth=3).to(cuda)
+    P = 40_000
+    xyz = synthetic.head_shell_points(P, g).to(cuda)
+    torch.manual_seed(4)
+    dec = SequentialDecoderReverse(StubG(planes, "panohead", 3), use_xyz_embedding=False, use_gen_finetune=False, device=cuda)
+    cam = synthetic_cam(cuda, 0.2)
+    bg = torch.tensor(synthetic.BG["panohead"], device=cuda)
+    pipe = FramePipeline(dec, P, 64, cuda)            # 16 tiles only
+    pipe.frame(planes, xyz, cam, bg)
+    _, redo = pipe.check()
+    assert not redo and pipe.bin_mode == 2
+    pipe.act["scale"].fill_(0.2)                       # every splat now covers the whole image: 16 lists of 40k
+    for _ in range(4):
+        img = pipe.render_only(cam, bg).clone()
+        R, redo = pipe.check()
+        if not redo:
+            break
+    assert not redo and pipe.bin_mode == 0 and R > 24576 * 16
+    s = rz.GaussianRasterizationSettings(64, 64, __import__("math").tan(cam.FoVx * 0.5), __import__("math").tan(cam.FoVy * 0.5), bg, 1.0,
+                                         cam.world_view_transform, cam.full_proj_transform, 0, cam.camera_center, False, False)
+    ref, _ = rz.GaussianRasterizer(s)(means3D=pipe.out["xyz"], means2D=torch.zeros_like(pipe.out["xyz"]), opacities=pipe.act["opacity"],
+                                      shs=pipe.out["color"][:, None, :].contiguous(), scales=pipe.act["scale"], rotations=pipe.act["rotation"])
+    assert torch.equal(img, ref)
