@@ -84,7 +84,7 @@ template <typename TOut>
 __global__ void __launch_bounds__(256)
 planes_channels_last_kernel(const float* __restrict__ src, TOut* __restrict__ dst, int D, int H, int W)
 {
-    __shared__ float tile[kFeat][kSlab + 4];
+    __shared__ __align__(16) float tile[kFeat][kSlab + 4];
     const size_t HW = (size_t)H * W;
     const size_t slabs_per_pd = (HW + kSlab - 1) / kSlab;
     const size_t slab = blockIdx.x;
@@ -104,13 +104,13 @@ planes_channels_last_kernel(const float* __restrict__ src, TOut* __restrict__ ds
             if (t + 2 < HW) v.z = __ldg(p + 2);
             if (t + 3 < HW) v.w = __ldg(p + 3);
         }
-        tile[c][4 * q] = v.x; tile[c][4 * q + 1] = v.y; tile[c][4 * q + 2] = v.z; tile[c][4 * q + 3] = v.w;
+        *reinterpret_cast<float4*>(&tile[c][4 * q]) = v;   // rows are 16-byte aligned (kSlab + 4 floats)
     }
     __syncthreads();
     constexpr int kPer = 16 / sizeof(TOut);              // channels per 16-byte store: 4 (fp32) or 8 (fp16)
     constexpr int kChunks = kFeat / kPer;
     for (int i = threadIdx.x; i < kSlab * kChunks; i += 256) {
-        const int tt = i / kChunks, ch = (i % kChunks) * kPer;
+        const int tt = i % kSlab, ch = (i / kSlab) * kPer;   // consecutive lanes = consecutive texels: conflict-free reads
         const size_t t = t0 + tt;
         if (t >= HW) continue;
         TOut* o = dst + (((size_t)plane * D + d) * HW + t) * kFeat + ch;
