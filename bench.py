@@ -73,6 +73,14 @@ class ClockSampler:
                 getattr(n, "nvmlClocksEventReasonSwThermalSlowdown", 0x20), getattr(n, "nvmlClocksEventReasonSwPowerCap", 0x4))
         self.rows.append([str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b in bits])
 
+    def sample_now(self):
+        """One sample from the calling thread (call it while the timed work is still queued on the GPU)."""
+        if self.nvml is not None:
+            try:
+                self._sample()
+            except Exception:
+                pass
+
     def _poll(self):
         while not self._stop.is_set():
             try:
@@ -177,6 +185,7 @@ def run_ours(args, rank, world, dev):
         for i in range(args.steps):
             pipe.frame(*dev_sets[i % len(dev_sets)], cam, bg)
         e1.record()
+        clk.sample_now()      # the steps are still executing: at least one sample under load even for a short region
         barrier()
     ms_total = e0.elapsed_time(e1)
     R, over = pipe.check()
