@@ -15,7 +15,7 @@
 //   preprocess        counts instances per tile (atomics, fused into the projection kernel)
 //   tile_scan_kernel  exclusive scan of the counts -> ranges[tile] = [start, end) ((0,0) for an empty
 //                     tile, as the reference leaves it); sets up each tile's write cursor; decides
-//                     whether the frame qualifies (longest list <= kTileSortMax,
+//                     whether the frame qualifies (longest list <= kTileSortLargeMax,
 //                     R <= capacity)
 //   tile_scatter      slot-centric like duplicate_kernel; claims a slot in the tile's segment with an
 //                     atomic on the tile's cursor
