@@ -11,6 +11,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libggd_b200.so")
 
 GGD_OK, GGD_E_INVALID, GGD_E_CUDA, GGD_E_CAPACITY = 0, 1, 2, 3
+ABI_VERSION = 2          # ggd_abi_version() of the library these signatures describe
+BINNING_RADIX, BINNING_AUTO, BINNING_TILES = 0, 1, 2
 
 
 class GGDError(RuntimeError):
@@ -44,10 +46,10 @@ SIGNATURES = {
     "ggd_abi_version": (_i, []),
     "ggd_raster_workspace_sizes": (_i, [_i, _i, _i, _u64, C.POINTER(_sz)]),
     "ggd_raster_preprocess": (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p,
-                                   _f, _f, _i, _p, _p, _p]),
-    "ggd_raster_render": (_i, [_p, _i, _i, _i, _p, _p, _p, _p, _p, _u64, _p, _p]),
+                                   _f, _f, _i, _p, _p, _p, _i]),
+    "ggd_raster_render": (_i, [_p, _i, _i, _i, _p, _p, _p, _p, _p, _u64, _p, _p, _i]),
     "ggd_raster_forward": (_i, [_p, _i, _i, _i, _p, _i, _i, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p,
-                                _f, _f, _i, _p, _p, _u64, _p, _p, _p, _p]),
+                                _f, _f, _i, _p, _p, _u64, _p, _p, _p, _p, _i]),
     "ggd_raster_backward": (_i, [_p, _i, _i, _i, _p, _i, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _p,
                                  _p, _p, _u64, _p] + [_p] * 10),
     "ggd_raster_status": (_i, [_p, _p, _i, C.POINTER(C.c_uint32)]),
@@ -91,6 +93,9 @@ def load():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
+    if lib.ggd_abi_version() != ABI_VERSION:
+        raise ImportError(f"{LIB_PATH} has ABI version {lib.ggd_abi_version()}, this binding needs {ABI_VERSION}: "
+                          "rebuild it (__graft_entry__.build())")
     _lib = lib
     return lib
 

@@ -12,43 +12,37 @@ import torch
 
 
 def getProjectionMatrix(znear, zfar, fovX, fovY):
-    tanHalfFovY = math.tan(fovY / 2)
-    tanHalfFovX = math.tan(fovX / 2)
-    top = tanHalfFovY * znear
-    bottom = -top
-    right = tanHalfFovX * znear
-    left = -right
-    P = torch.zeros(4, 4)
-    z_sign = 1.0
-    P[0, 0] = 2.0 * znear / (right - left)
-    P[1, 1] = 2.0 * znear / (top - bottom)
-    P[0, 2] = (right + left) / (right - left)
-    P[1, 2] = (top + bottom) / (top - bottom)
-    P[3, 2] = z_sign
-    P[2, 2] = z_sign * (zfar + znear) / (zfar - znear)
-    P[2, 3] = -(zfar * znear) / (zfar - znear)
-    return P
+    """OpenGL-style perspective matrix (column-vector convention, z_sign = +1, symmetric frustum) with the
+    reference's ``(f + n) / (f - n)`` depth term.  The entries are evaluated in Python doubles in the same order
+    as the reference does (near-plane half extents first) and rounded to fp32 once, so the matrix is bit-identical
+    to the reference's — pinned by tests/test_cameras.py against tests/golden/cameras.npz."""
+    half_w = math.tan(fovX / 2) * znear          # right = -left
+    half_h = math.tan(fovY / 2) * znear          # top = -bottom
+    depth = zfar - znear
+    return torch.tensor([[2.0 * znear / (half_w + half_w), 0.0, 0.0, 0.0],
+                         [0.0, 2.0 * znear / (half_h + half_h), 0.0, 0.0],
+                         [0.0, 0.0, (zfar + znear) / depth, -(zfar * znear) / depth],
+                         [0.0, 0.0, 1.0, 0.0]], dtype=torch.float32)
 
 
 class CustomCam:
-    """``extr`` is the EG3D cam2world matrix; ``fov`` is in radians (both axes)."""
+    """3DGS camera from an EG3D pose.  ``extr`` is the EG3D cam2world matrix (column vectors); ``fov`` is in
+    radians and applies to both axes.  Attribute names are the ones ``render_simple`` reads."""
 
     def __init__(self, size, fov, extr, znear=0.01, zfar=10.0):
-        self.image_width = size
-        self.image_height = size
-        self.FoVy = fov
-        self.FoVx = fov
-        self.znear = znear
-        self.zfar = zfar
-        # invert and transpose: EG3D column-vector c2w -> 3DGS row-vector w2c
-        self.world_view_transform = extr.T.inverse()
-        self.projection_matrix = getProjectionMatrix(
-            znear=self.znear, zfar=self.zfar, fovX=self.FoVx, fovY=self.FoVy).transpose(0, 1).to(extr.device)
-        self.full_proj_transform = (self.world_view_transform.unsqueeze(0).bmm(
-            self.projection_matrix.unsqueeze(0))).squeeze(0)
-        # NB: this is the w2c translation, not the camera position (reference quirk q6);
+        self.image_width = self.image_height = size
+        self.FoVx = self.FoVy = fov
+        self.znear, self.zfar = znear, zfar
+        # 3DGS kernels index matrices as m[4*col + row] of a row-vector world->camera transform:
+        # that is the inverse of the transposed cam2world
+        view = extr.T.inverse()
+        proj = getProjectionMatrix(znear, zfar, fov, fov).T.to(extr.device)
+        self.world_view_transform = view
+        self.projection_matrix = proj
+        self.full_proj_transform = torch.bmm(view[None], proj[None])[0]
+        # NB: row 3 of the view matrix is the w2c translation, not the camera position (reference quirk q6);
         # it only matters for SH degree > 0, which the decoder path never uses.
-        self.camera_center = self.world_view_transform[3, :3]
+        self.camera_center = view[3, :3]
 
 
 def look_at_cam2world(h, v, radius=2.7):

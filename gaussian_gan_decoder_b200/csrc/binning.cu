@@ -20,6 +20,7 @@
 //  * the element count lives in device memory; grids are sized by the buffer
 //    capacity and surplus CTAs exit, so no host round-trip is needed.
 #include "common.cuh"
+#include <atomic>
 #include <cstdlib>
 
 namespace ggd {
@@ -502,19 +503,29 @@ extern "C" int ggd_sort_pairs_static(void* stream, const uint64_t* keys_in, uint
     // Set-up, once per device, with that device current: in host code the array's name is only a
     // stand-in for the symbol, not a device address, so the address each GPU gave it is looked up
     // and remembered here and THAT pointer is what the kernels receive.
-    static void* scratch_on_device[kMaxDevices] = {nullptr};
+    static std::atomic<void*> scratch_on_device[kMaxDevices];
     int dev = -1;
     GGD_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev < 0 || dev >= kMaxDevices) {
         set_error("ggd_sort_pairs_static: device ordinal %d out of range", dev);
         return GGD_E_INVALID;
     }
-    if (!scratch_on_device[dev]) {
-        void* ptr = nullptr;
-        GGD_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_static_sort_scratch));
-        scratch_on_device[dev] = ptr;
+    // The address belongs to the CURRENT device; a stream of another device would hand its kernels a
+    // pointer into the wrong GPU.  (The legacy and per-thread default streams always follow the current device.)
+    if (stream != nullptr && stream != (void*)cudaStreamLegacy && stream != (void*)cudaStreamPerThread) {
+        int sdev = -1;
+        GGD_CUDA_CHECK(cudaStreamGetDevice(static_cast<cudaStream_t>(stream), &sdev));
+        if (sdev != dev) {
+            set_error("ggd_sort_pairs_static: stream belongs to device %d but device %d is current; "
+                      "make the stream's device current before the call", sdev, dev);
+            return GGD_E_INVALID;
+        }
     }
-    void* scratch = scratch_on_device[dev];
+    void* scratch = scratch_on_device[dev].load(std::memory_order_acquire);
+    if (!scratch) {   // two threads may both get here: they look up and store the same address
+        GGD_CUDA_CHECK(cudaGetSymbolAddress(&scratch, g_static_sort_scratch));
+        scratch_on_device[dev].store(scratch, std::memory_order_release);
+    }
     SortScratch sc = carve_sort_scratch(scratch, capacity);
     if (sc.bytes > kStaticSortBytes) {
         set_error("ggd_sort_pairs_static: internal scratch size mismatch (%zu > %zu)", sc.bytes, kStaticSortBytes);

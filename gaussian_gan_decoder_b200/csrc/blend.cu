@@ -174,8 +174,7 @@ int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const Geo
                  const BinState& b, const ImgState& im, const float* features,
                  const float* background, float* out_color)
 {
-    static int sms = 0;
-    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const int sms = device_sm_count();
     const char* e = getenv("GGD_BLEND_CTAS");
     const int per_sm = e ? atoi(e) : 6;
     const int tiles = grid_x * grid_y;

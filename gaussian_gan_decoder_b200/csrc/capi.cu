@@ -1,6 +1,7 @@
 // extern "C" entry points declared in include/ggd.h: argument validation,
 // state-buffer carving and stage orchestration.  No kernels live here.
 #include "common.cuh"
+#include <atomic>
 #include <cstdarg>
 #include <cstring>
 #include <algorithm>
@@ -18,19 +19,29 @@ void set_error(const char* fmt, ...)
 }
 
 // ---- stage timing ---------------------------------------------------------
-static bool g_timing = false;
-static cudaEvent_t g_ev[kStCount][2];
-static bool g_ev_made = false, g_ev_used[kStCount];
+// A benchmarking aid, off by default.  One event set per device; while it is on, drive each device from
+// one host thread and one stream at a time (the events of two interleaved frames would overwrite each other).
+static std::atomic<bool> g_timing{false};
+struct StageEvents { cudaEvent_t ev[kStCount][2]; bool made = false, used[kStCount]; };
+static StageEvents g_stage[64];
+static StageEvents* stage_events()
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    return &g_stage[dev];
+}
 
 void stage_mark(cudaStream_t s, int stage, bool begin)
 {
-    if (!g_timing) return;
-    if (!g_ev_made) {
-        for (int i = 0; i < kStCount; ++i) { cudaEventCreate(&g_ev[i][0]); cudaEventCreate(&g_ev[i][1]); g_ev_used[i] = false; }
-        g_ev_made = true;
+    if (!g_timing.load(std::memory_order_relaxed)) return;
+    StageEvents* e = stage_events();
+    if (!e) return;
+    if (!e->made) {
+        for (int i = 0; i < kStCount; ++i) { cudaEventCreate(&e->ev[i][0]); cudaEventCreate(&e->ev[i][1]); e->used[i] = false; }
+        e->made = true;
     }
-    cudaEventRecord(g_ev[stage][begin ? 0 : 1], s);
-    if (!begin) g_ev_used[stage] = true;
+    cudaEventRecord(e->ev[stage][begin ? 0 : 1], s);
+    if (!begin) e->used[stage] = true;
 }
 
 namespace {
@@ -115,17 +126,40 @@ size_t tiles_of(int W, int H) { return (size_t)((W + kTileX - 1) / kTileX) * (si
 // How stage 2a bins: 0 = global radix sort only, 1 = per tile when the frame qualifies (decided on the device,
 // both kernel sets enqueued), 2 = per tile only (a frame that does not qualify raises status flag 2).
 // Start-up value from GGD_BINNING ("radix" | "auto" | "tiles"), overridden by ggd_raster_binning().
-int g_binning = -1;
-int binning_mode()
+// That process-wide value is only the DEFAULT a call gets when it passes binning = -1; every raster entry
+// point takes the mode of its frame as an argument, so two callers never share it.
+std::atomic<int> g_binning{-1};
+int default_binning()
 {
-    if (g_binning < 0) {
+    int m = g_binning.load(std::memory_order_relaxed);
+    if (m < 0) {
         const char* e = getenv("GGD_BINNING");
-        g_binning = (e && e[0] == 'r') ? 0 : (e && e[0] == 't') ? 2 : 1;
+        m = (e && e[0] == 'r') ? 0 : (e && e[0] == 't') ? 2 : 1;
+        g_binning.store(m, std::memory_order_relaxed);
     }
-    return g_binning;
+    return m;
+}
+bool resolve_binning(int& mode, const char* who)
+{
+    if (mode == -1) mode = default_binning();
+    if (mode < 0 || mode > 2) { set_error("%s: binning must be -1 (default), 0, 1 or 2 (got %d)", who, mode); return false; }
+    return true;
 }
 
 }  // namespace
+
+int device_sm_count()
+{
+    static std::atomic<int> cache[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
+    int v = dev >= 0 ? cache[dev].load(std::memory_order_relaxed) : 0;
+    if (!v) {
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev < 0 ? 0 : dev) != cudaSuccess || v <= 0) v = 148;
+        if (dev >= 0) cache[dev].store(v, std::memory_order_relaxed);
+    }
+    return v;
+}
 }  // namespace ggd
 
 using namespace ggd;
@@ -134,13 +168,13 @@ extern "C" {
 
 int ggd_raster_binning(int mode)
 {
-    const int prev = binning_mode();
-    if (mode >= 0 && mode <= 2) g_binning = mode;
+    const int prev = default_binning();
+    if (mode >= 0 && mode <= 2) g_binning.store(mode, std::memory_order_relaxed);
     return prev;
 }
 
 const char* ggd_last_error(void) { return g_err; }
-int ggd_abi_version(void) { return 1; }
+int ggd_abi_version(void) { return 2; }
 
 int ggd_raster_workspace_sizes(int P, int W, int H, uint64_t bin_capacity, size_t sizes_out[3])
 {
@@ -158,9 +192,10 @@ int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int H,
                           const float* rotations, const float* cov3D_precomp,
                           const float* viewmatrix, const float* projmatrix, const float* campos,
                           float tan_fovx, float tan_fovy, int prefiltered,
-                          void* geom_ws, int* radii, uint32_t* num_rendered_host)
+                          void* geom_ws, int* radii, uint32_t* num_rendered_host, int binning)
 {
     if (int e = check_common(P, W, H)) return e;
+    if (!resolve_binning(binning, "ggd_raster_preprocess")) return GGD_E_INVALID;
     if (!means3D || !opacities || !viewmatrix || !projmatrix || !geom_ws) { set_error("ggd_raster_preprocess: null required pointer"); return GGD_E_INVALID; }
     if ((shs == nullptr) == (colors_precomp == nullptr)) { set_error("provide exactly one of shs / colors_precomp"); return GGD_E_INVALID; }
     if (((scales == nullptr) || (rotations == nullptr)) == (cov3D_precomp == nullptr)) { set_error("provide exactly one of (scales, rotations) / cov3D_precomp"); return GGD_E_INVALID; }
@@ -174,7 +209,8 @@ int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int H,
     if (!radii) radii = g.radii;
 
     PreprocessArgs a;
-    a.tile_counts = binning_mode() ? g.tile_counts : nullptr;
+    a.tile_counts = binning ? g.tile_counts : nullptr;
+    a.counts_valid = g.counters + 12;
     a.P = P; a.D = D; a.M = shs ? M : 0; a.W = W; a.H = H;
     a.means3D = means3D; a.shs = shs; a.colors_precomp = colors_precomp; a.opacities = opacities;
     a.scales = scales; a.scale_modifier = scale_modifier; a.rotations = rotations;
@@ -198,9 +234,10 @@ int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int H,
 int ggd_raster_render(void* stream, int P, int W, int H, const float* background,
                       const float* colors_precomp, const int* radii,
                       void* geom_ws, void* bin_ws, uint64_t bin_capacity, void* img_ws,
-                      float* out_color)
+                      float* out_color, int binning)
 {
     if (int e = check_common(P, W, H)) return e;
+    if (!resolve_binning(binning, "ggd_raster_render")) return GGD_E_INVALID;
     if (!background || !geom_ws || !bin_ws || !img_ws || !out_color) { set_error("ggd_raster_render: null required pointer"); return GGD_E_INVALID; }
     if (!aligned256(geom_ws) || !aligned256(bin_ws) || !aligned256(img_ws)) { set_error("state buffers must be 256-byte aligned"); return GGD_E_INVALID; }
     if (bin_capacity >= (1ull << 30)) { set_error("bin_capacity %llu exceeds 2^30-1", (unsigned long long)bin_capacity); return GGD_E_INVALID; }
@@ -212,8 +249,8 @@ int ggd_raster_render(void* stream, int P, int W, int H, const float* background
     if (!radii) radii = g.radii;
     const int grid_x = (W + kTileX - 1) / kTileX, grid_y = (H + kTileY - 1) / kTileY;
     const int tiles = grid_x * grid_y;
-    const bool per_tile = binning_mode() != 0 && bin_capacity > 0;
-    const bool radix = !(per_tile && binning_mode() == 2);   // enqueue the radix kernels
+    const bool per_tile = binning != 0 && bin_capacity > 0;
+    const bool radix = !(per_tile && binning == 2);   // enqueue the radix kernels
     const int end_bit = 32 + tile_key_bits((uint32_t)tiles);
     const int num_passes = (end_bit + kRadixBits - 1) / kRadixBits;
 
@@ -249,14 +286,15 @@ int ggd_raster_forward(void* stream, int P, int D, int M, const float* backgroun
                        const float* viewmatrix, const float* projmatrix, const float* campos,
                        float tan_fovx, float tan_fovy, int prefiltered,
                        void* geom_ws, void* bin_ws, uint64_t bin_capacity, void* img_ws,
-                       float* out_color, int* radii, uint32_t* num_rendered_host)
+                       float* out_color, int* radii, uint32_t* num_rendered_host, int binning)
 {
+    if (!resolve_binning(binning, "ggd_raster_forward")) return GGD_E_INVALID;
     if (int e = ggd_raster_preprocess(stream, P, D, M, W, H, means3D, shs, colors_precomp, opacities,
                                       scales, scale_modifier, rotations, cov3D_precomp, viewmatrix,
                                       projmatrix, campos, tan_fovx, tan_fovy, prefiltered, geom_ws,
-                                      radii, num_rendered_host)) return e;
+                                      radii, num_rendered_host, binning)) return e;
     return ggd_raster_render(stream, P, W, H, background, colors_precomp, radii, geom_ws, bin_ws,
-                             bin_capacity, img_ws, out_color);
+                             bin_capacity, img_ws, out_color, binning);
 }
 
 int ggd_raster_status(void* stream, const void* geom_ws, int P, uint32_t out[2])
@@ -320,16 +358,18 @@ int ggd_raster_field(int which, const char* name, int P, int W, int H, uint64_t 
     return GGD_E_INVALID;
 }
 
-int ggd_stage_timing(int enable) { g_timing = enable != 0; return GGD_OK; }
+int ggd_stage_timing(int enable) { g_timing.store(enable != 0); return GGD_OK; }
 
 int ggd_stage_times(float ms_out[8])
 {
     if (!ms_out) { set_error("ggd_stage_times: null pointer"); return GGD_E_INVALID; }
+    StageEvents* e = stage_events();
     for (int i = 0; i < kStCount; ++i) {
         ms_out[i] = -1.f;
-        if (g_ev_made && g_ev_used[i]) {
-            GGD_CUDA_CHECK(cudaEventSynchronize(g_ev[i][1]));
-            GGD_CUDA_CHECK(cudaEventElapsedTime(&ms_out[i], g_ev[i][0], g_ev[i][1]));
+        if (e && e->made && e->used[i]) {
+            GGD_CUDA_CHECK(cudaEventSynchronize(e->ev[i][1]));
+            GGD_CUDA_CHECK(cudaEventElapsedTime(&ms_out[i], e->ev[i][0], e->ev[i][1]));
+            e->used[i] = false;   // a stage that does not run in the next frame reads -1, not a stale time
         }
     }
     return GGD_OK;

@@ -43,6 +43,9 @@ constexpr int kTilePixels = kTileX * kTileY;
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// SM count of the CURRENT device (cached per device ordinal, capi.cu)
+int device_sm_count();
+
 // ---- radix sort geometry (binning.cu) -------------------------------------
 constexpr int kRadixBits = 8;
 constexpr int kRadixBins = 1 << kRadixBits;
@@ -80,7 +83,9 @@ struct GeomState {
     uint8_t* clamped;         // [P][3]
     uint32_t* counters;       // [0] num_rendered, [1] overflow flag, [2] scan ticket, [3] clamped count,
                               // [4] 1 = this frame is binned per tile (tile_binning.cu), [5] longest tile list,
-                              // [6] element count the radix kernels see, [7] number of tile lists > kTileSortMax
+                              // [6] element count the radix kernels see, [7] number of tile lists > kTileSortMax,
+                              // [8], [10] tile queues of the blend kernels, [12] 1 = preprocess counted tile_counts
+                              // for this frame (so stage 2 never trusts counts that were not written)
     uint64_t* scan_status;    // [scan tiles] decoupled look-back words of the scan
     uint32_t* tile_counts;    // [tiles][kTileCountStride] word 0: instances per tile, counted by preprocess; word 2: the
                               // tile's write cursor; word 1 of entry i: id of the i-th long tile list.  One 128-byte
@@ -130,6 +135,7 @@ struct PreprocessArgs {
     int prefiltered;
     int grid_x, grid_y;
     uint32_t* tile_counts;   // optional [grid_x * grid_y][32]: word 0 += 1 for every tile a splat touches
+    uint32_t* counts_valid;  // set to 1 by the kernel when tile_counts were written (GeomState::counters[12])
 };
 int launch_preprocess(cudaStream_t s, const PreprocessArgs& a, const GeomState& g, int* radii);
 int launch_scan(cudaStream_t s, int P, const GeomState& g);

@@ -161,6 +161,7 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
     const bool have_cov = a.cov3D_precomp != nullptr;
     const bool have_col = a.colors_precomp != nullptr;
     const bool sh_staged = !have_col && a.M == 1;
+    if (a.tile_counts && blockIdx.x == 0 && t == 0) *a.counts_valid = 1u;
 
     block_load(s_xyz, a.means3D + (size_t)base * 3, n_here * 3);
     if (have_cov) block_load(s_cov, a.cov3D_precomp + (size_t)base * 6, n_here * 6);

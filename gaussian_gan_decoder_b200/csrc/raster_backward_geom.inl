@@ -232,8 +232,7 @@ extern "C" int ggd_raster_backward(void* stream, int P, int D, int M, const floa
     const float* colors = colors_precomp ? colors_precomp : g.rgb;
     // the state buffers are inputs here except for two words of the geometry state's counter block, which serve as the
     // (self-resetting) tile queue of the persistent kernel
-    static int sms = 0;
-    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const int sms = device_sm_count();
     const int tiles = grid_x * grid_y;
     blend_backward_kernel<<<tiles < 4 * sms ? tiles : 4 * sms, kTilePixels, 0, s>>>(
         im.ranges, b.vals, W, H, background, g.means2D, g.conic_opacity, colors, im.accum_alpha, im.n_contrib,

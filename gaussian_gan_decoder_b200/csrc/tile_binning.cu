@@ -50,7 +50,9 @@ tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int 
         uint32_t m = 0;
         for (int w = 0; w < kScanThreadsT / 32; ++w) m = max(m, s_warp[w]);
         const uint32_t R = P > 0 ? __ldg(offsets + P - 1) : 0u;
-        const bool per_tile = m <= kTileSortLargeMax && R <= capacity;
+        // counters[12]: preprocess counted the tile lists of THIS frame (it does so only when asked to); without it
+        // the counts are the zeros of the frame's memset and must not be taken for an empty frame
+        const bool per_tile = counters[12] != 0u && m <= kTileSortLargeMax && R <= capacity;
         s_max = per_tile ? 1u : 0u;
         s_carry = 0;
         s_large = 0;
@@ -93,7 +95,11 @@ tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int 
         if (t == kScanThreadsT - 1) s_carry = off + incl;
         __syncthreads();
     }
-    if (t == 0) counters[7] = s_large;
+    if (t == 0) {
+        counters[7] = s_large;
+        // flag 4: the per-tile counts do not add up to R (state buffers of two different frames were mixed)
+        if (s_carry != counters[3]) counters[1] |= 4u;
+    }
 }
 
 constexpr int kScatterThreads = 256;

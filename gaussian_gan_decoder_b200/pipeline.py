@@ -30,8 +30,9 @@ class FramePipeline:
         self.capacity = None
         self.geom = self.binning = self.img = None
         self.pinned = torch.zeros(4, dtype=torch.int32).pin_memory()
-        # stage-2 binning mode of this loop (ggd_raster_binning): starts at the library's setting; check() moves
-        # it to 2 (tiles only: no radix launches) once a frame qualified, and back to 1 if one did not.
+        # stage-2 binning mode of this loop, passed with every call (this pipeline's own: another pipeline or thread
+        # cannot change it): starts at the library default; check() moves it to 2 (tiles only: no radix launches)
+        # once a frame qualified, and back to 1 if one did not.
         self.bin_mode = self.lib.ggd_raster_binning(-1)
         self._alloc(capacity or 4 * P)
 
@@ -69,17 +70,13 @@ class FramePipeline:
     def _raster(self, s, cam, bg):
         import math
         lib, p, P = self.lib, _lib.ptr, self.P
-        prev = lib.ggd_raster_binning(self.bin_mode)
-        try:
-            _lib.check(lib.ggd_raster_forward(
-                s, P, 0, 1, p(bg), self.W, self.H, p(self.out["xyz"]), p(self.out["color"]), None,
-                p(self.act["opacity"]), p(self.act["scale"]), 1.0, p(self.act["rotation"]), None,
-                p(cam.world_view_transform), p(cam.full_proj_transform), p(cam.camera_center),
-                math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), 0,
-                p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
-                C.c_void_p(self.pinned.data_ptr())))
-        finally:
-            lib.ggd_raster_binning(prev)
+        _lib.check(lib.ggd_raster_forward(
+            s, P, 0, 1, p(bg), self.W, self.H, p(self.out["xyz"]), p(self.out["color"]), None,
+            p(self.act["opacity"]), p(self.act["scale"]), 1.0, p(self.act["rotation"]), None,
+            p(cam.world_view_transform), p(cam.full_proj_transform), p(cam.camera_center),
+            math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), 0,
+            p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
+            C.c_void_p(self.pinned.data_ptr()), self.bin_mode))
 
     def capture(self, planes_nchw, xyz, cam, bg):
         """Record one frame (planes -> decode -> rasterise) into a CUDA graph.  The graph reads the given

@@ -17,6 +17,7 @@ Differences that a caller can observe:
 """
 from typing import NamedTuple
 import ctypes as C
+import threading
 
 import torch
 import torch.nn as nn
@@ -53,14 +54,20 @@ def _stream():
 
 # instance-count guess per (device, P, H, W): drives the binning-buffer capacity
 _capacity_hint = {}
-_pinned = {}
+_tls = threading.local()
 
 
 def _pinned_u32(device):
+    """Pinned word the frame's instance count is copied into.  One per host thread and device: a call
+    synchronises its stream before it returns, so the word is free again when the thread's next call
+    starts, and two threads never share one."""
     key = device.index if device.index is not None else torch.cuda.current_device()
-    if key not in _pinned:
-        _pinned[key] = torch.zeros(4, dtype=torch.int32).pin_memory()
-    return _pinned[key]
+    words = getattr(_tls, "words", None)
+    if words is None:
+        words = _tls.words = {}
+    if key not in words:
+        words[key] = torch.zeros(4, dtype=torch.int32).pin_memory()
+    return words[key]
 
 
 def workspace_sizes(P, W, H, capacity):
@@ -113,6 +120,7 @@ class _CNamespace:
         # Stage-2 binning (ggd_raster_binning): counting instances per tile costs one atomic per (splat, tile),
         # wasted on frames whose tile lists are too long for the per-tile path.  Remember per shape whether
         # the last frame qualified; a shape that did not is rendered radix-only and probed again now and then.
+        # The mode travels with the call (an argument of both stages), never through process state.
         lib_mode = lib.ggd_raster_binning(-1)
         bh = _binning_hint.setdefault(key, [min(lib_mode, 1), 0])
         mode = bh[0] if lib_mode else 0
@@ -120,49 +128,45 @@ class _CNamespace:
             bh[1] += 1
             if bh[1] % 64 == 0:
                 mode = 1
-        lib.ggd_raster_binning(mode)
         pinned = _pinned_u32(dev)
         host_R = C.c_void_p(pinned.data_ptr())
-        try:
-            with torch.cuda.device(dev):
-                s = _stream()
-                geom_b, _, img_b = workspace_sizes(P, W, H, 0)
-                geom = torch.empty(geom_b, dtype=torch.uint8, device=dev)
-                img = torch.empty(img_b, dtype=torch.uint8, device=dev)
-                pre_args = (s, P, int(degree), M, W, H, p(means3D), p(sh), p(colors), p(opacity), p(scales),
-                            float(scale_modifier), p(rotations), p(cov3D_precomp), p(viewmatrix), p(projmatrix),
-                            p(campos), float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
-                            p(geom), p(radii), host_R)
+        with torch.cuda.device(dev):
+            s = _stream()
+            geom_b, _, img_b = workspace_sizes(P, W, H, 0)
+            geom = torch.empty(geom_b, dtype=torch.uint8, device=dev)
+            img = torch.empty(img_b, dtype=torch.uint8, device=dev)
+            pre_args = (s, P, int(degree), M, W, H, p(means3D), p(sh), p(colors), p(opacity), p(scales),
+                        float(scale_modifier), p(rotations), p(cov3D_precomp), p(viewmatrix), p(projmatrix),
+                        p(campos), float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
+                        p(geom), p(radii), host_R, mode)
 
-                def render(cap):
-                    binning = torch.empty(workspace_sizes(P, W, H, cap)[1], dtype=torch.uint8, device=dev)
-                    _lib.check(lib.ggd_raster_render(s, P, W, H, p(background), p(colors), p(radii), p(geom),
-                                                     p(binning), cap, p(img), p(out_color)))
-                    return binning
+            def render(cap):
+                binning = torch.empty(workspace_sizes(P, W, H, cap)[1], dtype=torch.uint8, device=dev)
+                _lib.check(lib.ggd_raster_render(s, P, W, H, p(background), p(colors), p(radii), p(geom),
+                                                 p(binning), cap, p(img), p(out_color), mode))
+                return binning
 
-                _lib.check(lib.ggd_raster_preprocess(*pre_args))
-                if hint is None:
-                    torch.cuda.current_stream().synchronize()       # first frame of this shape only
-                    R = int(pinned[0].item()) & 0xffffffff
-                    cap = max(R, 1)
+            _lib.check(lib.ggd_raster_preprocess(*pre_args))
+            if hint is None:
+                torch.cuda.current_stream().synchronize()       # first frame of this shape only
+                R = int(pinned[0].item()) & 0xffffffff
+                cap = max(R, 1)
+                binning = render(cap)
+            else:
+                cap = hint
+                binning = render(cap)
+                torch.cuda.current_stream().synchronize()       # end of frame, nothing queued behind it
+                R = int(pinned[0].item()) & 0xffffffff
+                if R > cap:                                     # guess too small: redo binning + blend
+                    cap = R
                     binning = render(cap)
-                else:
-                    cap = hint
-                    binning = render(cap)
-                    torch.cuda.current_stream().synchronize()       # end of frame, nothing queued behind it
-                    R = int(pinned[0].item()) & 0xffffffff
-                    if R > cap:                                     # guess too small: redo binning + blend
-                        cap = R
-                        binning = render(cap)
-                if debug:
-                    torch.cuda.current_stream().synchronize()
-                _capacity_hint[key] = max(int(R * 1.25) + 4096, 4096)
-                if mode:
-                    info = (C.c_uint32 * 2)()
-                    _lib.check(lib.ggd_raster_binning_info(s, p(geom), P, info))
-                    bh[0] = 1 if info[0] else 0
-        finally:
-            lib.ggd_raster_binning(lib_mode)
+            if debug:
+                torch.cuda.current_stream().synchronize()
+            _capacity_hint[key] = max(int(R * 1.25) + 4096, 4096)
+            if mode:
+                info = (C.c_uint32 * 2)()
+                _lib.check(lib.ggd_raster_binning_info(s, p(geom), P, info))
+                bh[0] = 1 if info[0] else 0
         # capacity travels with the buffer so backward can re-carve it
         binning.ggd_capacity = cap
         return R, out_color, radii, geom, binning, img

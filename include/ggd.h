@@ -67,14 +67,18 @@ GGD_API int ggd_raster_workspace_sizes(int P, int W, int H, uint64_t bin_capacit
  * non-NULL.  `radii` may be NULL (an internal array is used).
  * `num_rendered_host`, if non-NULL, receives the instance count R through an
  * asynchronous device→host copy on `stream` (valid after the stream is
- * synchronised; use pinned memory to keep the copy asynchronous). */
+ * synchronised; use pinned memory to keep the copy asynchronous).
+ * `binning`: how stage 2 will order this frame's instances (GGD_BINNING_* below);
+ * in modes 1 and 2 this stage also counts the instances per tile and marks the
+ * geometry state accordingly, so ggd_raster_render can never mistake a state
+ * that was prepared without counts for an empty frame. */
 GGD_API int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int H,
                           const float* means3D, const float* shs, const float* colors_precomp,
                           const float* opacities, const float* scales, float scale_modifier,
                           const float* rotations, const float* cov3D_precomp,
                           const float* viewmatrix, const float* projmatrix, const float* campos,
                           float tan_fovx, float tan_fovy, int prefiltered,
-                          void* geom_ws, int* radii, uint32_t* num_rendered_host);
+                          void* geom_ws, int* radii, uint32_t* num_rendered_host, int binning);
 
 /* Stage 2: key duplication, radix sort, tile ranges, blending.  Replaces
  * duplicateWithKeys (rasterizer_impl.cu:70-111), getHigherMsb (:35-50),
@@ -83,11 +87,13 @@ GGD_API int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int 
  * (forward.cu:261-400).  R is read from geom_ws ON THE DEVICE; if R exceeds
  * bin_capacity nothing past the capacity is written, the overflow flag in
  * geom_ws is raised (see ggd_raster_status) and the image is undefined — the
- * caller re-runs this stage with a larger binning buffer. */
+ * caller re-runs this stage with a larger binning buffer.  `binning` should be the
+ * mode stage 1 ran under; mode 1 on a state prepared in mode 0 falls back to the
+ * radix sort on the device, mode 2 on such a state raises status flag 2. */
 GGD_API int ggd_raster_render(void* stream, int P, int W, int H, const float* background,
                       const float* colors_precomp, const int* radii,
                       void* geom_ws, void* bin_ws, uint64_t bin_capacity, void* img_ws,
-                      float* out_color);
+                      float* out_color, int binning);
 
 /* Stages 1+2 back to back on `stream`, no host synchronisation.  Replaces
  * CudaRasterizer::Rasterizer::forward (rasterizer_impl.cu:198-337). */
@@ -98,7 +104,7 @@ GGD_API int ggd_raster_forward(void* stream, int P, int D, int M, const float* b
                        const float* viewmatrix, const float* projmatrix, const float* campos,
                        float tan_fovx, float tan_fovy, int prefiltered,
                        void* geom_ws, void* bin_ws, uint64_t bin_capacity, void* img_ws,
-                       float* out_color, int* radii, uint32_t* num_rendered_host);
+                       float* out_color, int* radii, uint32_t* num_rendered_host, int binning);
 
 /* Backward of ggd_raster_forward.  Replaces CudaRasterizer::Rasterizer::backward
  * (DGR/cuda_rasterizer/rasterizer_impl.cu:340-435): BACKWARD::render -> renderCUDA
@@ -121,21 +127,31 @@ GGD_API int ggd_raster_backward(void* stream, int P, int D, int M, const float* 
                                 float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                                 float* dL_dscale, float* dL_drot);
 
-/* Blocking read-back of { num_rendered, overflow_flag } from geom_ws
- * (synchronises `stream`).  The reference returns num_rendered from forward
+/* Blocking read-back of { num_rendered, flags } from geom_ws (synchronises `stream`).  flags: 1 = more
+ * instances than bin_capacity, 2 = mode 2 frame that needs the radix kernels, 4 = the per-tile counts in
+ * geom_ws do not add up to num_rendered (state buffers of different frames were mixed); with any flag
+ * set the image is undefined.  The reference returns num_rendered from forward
  * (rasterizer_impl.cu:336); here it is a separate, optional query. */
 GGD_API int ggd_raster_status(void* stream, const void* geom_ws, int P, uint32_t out[2]);
 
-/* How stage 2 orders the instances.  mode 1 (default; env GGD_BINNING=auto): frames whose longest tile
- * list is at most 4096 are binned per tile and each list is sorted in shared memory
- * (csrc/tile_binning.cu); other frames take the global radix sort.  mode 0 (GGD_BINNING=radix): always
- * the radix sort.  Both produce the bits of the reference's duplicateWithKeys + stable SortPairs +
- * identifyTileRanges (rasterizer_impl.cu:70-138, :303-318).  The per-frame choice is made on the
- * device.  mode 2 (GGD_BINNING=tiles): like 1 but the radix kernels are not even enqueued (saves their
- * launches); a frame that turns out to need them raises flag 2 in ggd_raster_status's second word, its
- * image is undefined and the caller runs it again in mode 1 -- for frame loops whose scenes are known
- * to qualify.  Pass -1 to query.  Returns the previous mode.  Process-wide; the state buffers of a
- * frame must be rendered with the mode its preprocess call ran under.  No reference counterpart. */
+/* How stage 2 orders the instances — the `binning` argument of the three entry points above.
+ * GGD_BINNING_AUTO (1): frames whose longest tile list is at most 24576 are binned per tile and each
+ * list is sorted in shared memory (csrc/tile_binning.cu); other frames take the global radix sort;
+ * the per-frame choice is made on the device.  GGD_BINNING_RADIX (0): always the radix sort.  Both
+ * produce the bits of the reference's duplicateWithKeys + stable SortPairs + identifyTileRanges
+ * (rasterizer_impl.cu:70-138, :303-318).  GGD_BINNING_TILES (2): like 1 but the radix kernels are not
+ * even enqueued (saves their launches); a frame that turns out to need them raises flag 2 in
+ * ggd_raster_status's second word, its image is undefined and the caller runs it again in mode 1 --
+ * for frame loops whose scenes are known to qualify.  GGD_BINNING_DEFAULT (-1): the process default,
+ * which starts from env GGD_BINNING=radix|auto|tiles (auto if unset).
+ * The mode is an argument of each call (it used to be process-wide state: two callers could change it
+ * under each other between stage 1 and stage 2).  No reference counterpart. */
+#define GGD_BINNING_DEFAULT (-1)
+#define GGD_BINNING_RADIX 0
+#define GGD_BINNING_AUTO 1
+#define GGD_BINNING_TILES 2
+/* Sets the process DEFAULT used by calls that pass GGD_BINNING_DEFAULT; pass -1 to query.  Returns the
+ * previous default. */
 GGD_API int ggd_raster_binning(int mode);
 
 /* Blocking read-back of { binned_per_tile, longest_tile_list } of the last frame in geom_ws

@@ -57,6 +57,18 @@ class RefCuda:
             getattr(self.lib, n).argtypes = [C.c_size_t, C.POINTER(C.c_size_t)]
         self.lib.ggd_ref_read.restype = _i
         self.lib.ggd_ref_read.argtypes = [_i, C.c_size_t, _p, C.c_size_t]
+        self.lib.ggd_ref_mark_visible.restype = None
+        self.lib.ggd_ref_mark_visible.argtypes = [_i, _p, _p, _p, _p]
+
+    def mark_visible(self, means3D, viewmatrix, projmatrix):
+        """Reference CudaRasterizer::Rasterizer::markVisible (rasterizer_impl.cu:141-152) -> bool[P] (device)."""
+        P = means3D.shape[0]
+        present = torch.zeros(P, dtype=torch.bool, device=means3D.device)
+        m, v, pr = means3D.contiguous().float(), viewmatrix.contiguous().float(), projmatrix.contiguous().float()
+        torch.cuda.synchronize()
+        self.lib.ggd_ref_mark_visible(P, self._dp(m), self._dp(v), self._dp(pr), C.c_void_p(present.data_ptr()))
+        torch.cuda.synchronize()
+        return present
 
     @staticmethod
     def _dp(t):

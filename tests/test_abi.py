@@ -48,7 +48,7 @@ def test_bad_arguments_fail_loudly_without_a_gpu():
     assert b"2^30" in lib.ggd_last_error()
     # P <= 0 and null pointers are rejected before any CUDA call
     assert lib.ggd_raster_preprocess(None, 0, 0, 1, 64, 64, *([None] * 5), 1.0, *([None] * 5), 1.0, 1.0, 0,
-                                     None, None, None) == _lib.GGD_E_INVALID
+                                     None, None, None, -1) == _lib.GGD_E_INVALID
     with pytest.raises(_lib.GGDError):
         _lib.check(lib.ggd_mark_visible(None, 5, None, None, None, None))
 

@@ -113,3 +113,52 @@ def test_pipeline_recovers_when_a_frame_stops_qualifying(cuda):
     ref, _ = rz.GaussianRasterizer(s)(means3D=pipe.out["xyz"], means2D=torch.zeros_like(pipe.out["xyz"]), opacities=pipe.act["opacity"],
                                       shs=pipe.out["color"][:, None, :].contiguous(), scales=pipe.act["scale"], rotations=pipe.act["rotation"])
     assert torch.equal(img, ref)
+
+
+def test_two_host_threads_two_pipelines_different_binning_modes(cuda):
+    """Two host threads drive two FramePipelines on two streams, one pinned to the radix sort and one to
+    tiles-only binning, frames interleaving freely.  Each image must be bit-identical to the serial run:
+    nothing on the hot path is process-global any more (binning mode, pinned instance-count word, SM count)."""
+    import threading
+    g = synthetic.gen(12)
+    planes = synthetic.planes("panohead", g, res=64, depth=3).to(cuda)
+    P = 60_000
+    xyzs = [synthetic.head_shell_points(P, g).to(cuda) for _ in range(2)]
+    torch.manual_seed(6)
+    dec = SequentialDecoderReverse(StubG(planes, "panohead", 3), use_xyz_embedding=False, use_gen_finetune=False, device=cuda)
+    cams = [synthetic_cam(cuda, 0.0), synthetic_cam(cuda, 0.4)]
+    bg = torch.tensor(synthetic.BG["panohead"], device=cuda)
+    pipes = [FramePipeline(dec, P, 256, cuda) for _ in range(2)]
+    modes = (0, 2)
+    serial = []
+    for k in range(2):
+        pipes[k].bin_mode = modes[k]
+        pipes[k].frame(planes, xyzs[k], cams[k], bg)
+        R, redo = pipes[k].check()
+        assert not redo and R > 0 and pipes[k].bin_mode == modes[k]
+        serial.append(pipes[k].image.clone())
+    assert not torch.equal(serial[0], serial[1])
+    torch.cuda.synchronize()
+    errors = []
+
+    def worker(k):
+        try:
+            torch.cuda.set_device(cuda)
+            st = torch.cuda.Stream(device=cuda)
+            with torch.cuda.stream(st):
+                for _ in range(40):
+                    img = pipes[k].frame(planes, xyzs[k], cams[k], bg)
+                    R, redo = pipes[k].check()
+                    assert not redo and pipes[k].bin_mode == modes[k]
+                    if not torch.equal(img, serial[k]):
+                        errors.append((k, "image differs from the serial run"))
+                        return
+        except Exception as e:   # surfaced in the main thread
+            errors.append((k, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors

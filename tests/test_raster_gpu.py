@@ -89,6 +89,37 @@ def test_bit_exact_full_size_config2(cuda):
 
 
 @pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("mode", [0, 1])
+def test_bit_exact_config5_2048_2M(cuda, mode):
+    """BASELINE configs[4]: 2M trained-like Gaussians at 2048x2048 (16384 tiles -> 47-bit keys, ~2.8e8 instances,
+    tile lists beyond the per-tile path's 24576 limit, the large-capacity digit pass) — every integer and float
+    stage bit for bit against the reference CUDA build, with the radix sort pinned (mode 0) and with the
+    device-side choice (mode 1).  Follows rasterizer_impl.cu:300-308 (getHigherMsb, sort bit range) and
+    forward.cu:261-374."""
+    lib = _lib.load()
+    P = 2_000_000
+    s = to_dev(synthetic.raster_scene(P, size=2048, fov_deg=12.0, seed_offset=50), cuda)
+    ref = RefCuda().forward(s, cuda)
+    assert ref["R"] > 100_000_000
+    from gaussian_gan_decoder_b200 import rasterizer as rz
+    rz._binning_hint.pop((cuda.index, P, 2048, 2048), None)     # forget what an earlier run learnt about this shape
+    prev = lib.ggd_raster_binning(mode)
+    try:
+        ours = run_ours(s, cuda)
+        info = (C.c_uint32 * 2)()
+        _lib.check(lib.ggd_raster_binning_info(None, C.c_void_p(ours["_buffers"][0].data_ptr()), P, info))
+    finally:
+        lib.ggd_raster_binning(prev)
+    assert_bit_exact(ours, ref, P)
+    rng = ours["ranges"].view(-1, 2).long()
+    assert rng.shape[0] == 128 * 128 and int((rng[:, 1] - rng[:, 0]).max()) > 24576
+    if mode == 1:
+        assert info[0] == 0 and info[1] > 24576      # counted per tile, found too long, radix path taken on the device
+    del ours, ref
+    torch.cuda.empty_cache()
+
+
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
 def test_bit_exact_many_random_gaussians_preprocess(cuda):
     """>= 10^7 random Gaussians through the projection stage: zero integer mismatches."""
     ref_lib = RefCuda()
@@ -237,6 +268,13 @@ def test_sort_pairs_sizes(cuda, n):
     _sort_case(cuda, n, 0, 43, seed=n)
 
 
+@pytest.mark.parametrize("n,cap,end", [(4_194_304, 4_194_304, 47), (5_000_001, 6_000_000, 47), (4_500_000, 4_500_000, 43)])
+def test_sort_pairs_large_capacity_variant(cuda, n, cap, end):
+    """capacity >= 4 Mi pairs selects the 4-CTAs-per-SM digit pass (onesweep_kernel<4>, binning.cu); 47 key bits
+    are what a 2048^2 frame sorts on (32 depth bits + getHigherMsb(16384 tiles) = 15)."""
+    _sort_case(cuda, n, 0, end, seed=n % 1000 + 2, cap=cap)
+
+
 @pytest.mark.parametrize("begin,end", [(0, 8), (0, 64), (5, 17), (32, 47), (0, 1), (3, 44)])
 def test_sort_pairs_bit_ranges(cuda, begin, end):
     _sort_case(cuda, 50_000, begin, end, seed=begin * 64 + end)
@@ -264,6 +302,23 @@ def test_mark_visible(cuda):
     z = pts @ view[:3, 2] + view[3, 2]
     expect = z > 0.2
     assert vis.dtype == torch.bool and int((vis != expect).sum()) <= 2
+
+
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+def test_mark_visible_bit_exact_vs_reference_cuda(cuda):
+    """markVisible against the reference's own kernel (rasterizer_impl.cu:54-66, 141-152), including
+    points behind the camera, on the z = 0.2 cut and far outside the frustum."""
+    from gaussian_gan_decoder_b200.rasterizer import GaussianRasterizer, GaussianRasterizationSettings
+    s = to_dev(synthetic.raster_scene(300_001, size=512, seed_offset=21), cuda)
+    g = synthetic.gen(22)
+    spread = (torch.randn(300_001, 3, generator=g) * torch.tensor([1.0, 1.0, 4.0])).to(cuda)
+    pts = torch.cat([s["means3D"], s["means3D"] + spread])
+    rs = GaussianRasterizationSettings(512, 512, s["tanfovx"], s["tanfovy"], s["bg"], 1.0, s["viewmatrix"],
+                                       s["projmatrix"], 0, s["campos"], False, False)
+    ours = GaussianRasterizer(rs).markVisible(pts)
+    ref = RefCuda().mark_visible(pts, s["viewmatrix"], s["projmatrix"])
+    assert 0 < int(ref.sum()) < pts.shape[0]
+    assert torch.equal(ours, ref)
 
 
 @pytest.mark.parametrize("P,size,trained,expect_per_tile", [
@@ -337,8 +392,54 @@ def test_stage2_rerun_on_same_geometry_state(cuda):
             geom, binning, img = first["_buffers"]
             again = torch.zeros_like(first["out_color"])
             _lib.check(lib.ggd_raster_render(None, P, size, size, p(s["bg"]), None, p(first["radii"]), p(geom), p(binning),
-                                             first["capacity"], p(img), p(again)))
+                                             first["capacity"], p(img), p(again), mode))
             torch.cuda.synchronize()
         finally:
             lib.ggd_raster_binning(prev)
         assert torch.equal(again, first["out_color"])
+
+
+def _split_frame(lib, s, cuda, pre_mode, render_mode):
+    """Stage 1 and stage 2 through the C ABI with separately chosen binning modes."""
+    from gaussian_gan_decoder_b200 import rasterizer as rz
+    P, W, H = s["means3D"].shape[0], s["W"], s["H"]
+    p = _lib.ptr
+    cap = 16 * P
+    gb, bb, ib = rz.workspace_sizes(P, W, H, cap)
+    u8 = dict(dtype=torch.uint8, device=cuda)
+    geom, binning, img = torch.empty(gb, **u8), torch.empty(bb, **u8), torch.empty(ib, **u8)
+    radii = torch.zeros(P, dtype=torch.int32, device=cuda)
+    image = torch.zeros(3, H, W, device=cuda)
+    _lib.check(lib.ggd_raster_preprocess(None, P, 0, 1, W, H, p(s["means3D"]), p(s["shs"]), None, p(s["opacities"]),
+                                         p(s["scales"]), 1.0, p(s["rotations"]), None, p(s["viewmatrix"]),
+                                         p(s["projmatrix"]), p(s["campos"]), s["tanfovx"], s["tanfovy"], 0,
+                                         p(geom), p(radii), None, pre_mode))
+    _lib.check(lib.ggd_raster_render(None, P, W, H, p(s["bg"]), None, p(radii), p(geom), p(binning), cap, p(img),
+                                     p(image), render_mode))
+    st = (C.c_uint32 * 2)()
+    _lib.check(lib.ggd_raster_status(None, p(geom), P, st))
+    info = (C.c_uint32 * 2)()
+    _lib.check(lib.ggd_raster_binning_info(None, p(geom), P, info))
+    return image, st[0], st[1], info[0]
+
+
+def test_binning_mode_mismatch_between_stages_is_safe(cuda):
+    """The mode is an argument of each stage.  A geometry state prepared WITHOUT per-tile counts (mode 0)
+    and rendered in mode 1 must take the radix sort (same image), not read the zeroed counts as an empty
+    frame; rendered in mode 2 it must raise status flag 2.  (this used to render background only.)"""
+    lib = _lib.load()
+    s = to_dev(synthetic.raster_scene(30_000, size=256, seed_offset=8), cuda)
+    ref, R, flags, per_tile = _split_frame(lib, s, cuda, 1, 1)
+    assert R > 0 and flags == 0 and per_tile == 1
+    assert float((ref - s["bg"].view(3, 1, 1)).abs().max()) > 0.05     # something was drawn
+    img, R2, flags, per_tile = _split_frame(lib, s, cuda, 0, 1)
+    assert R2 == R and flags == 0 and per_tile == 0
+    assert torch.equal(img, ref)
+    img, R2, flags, per_tile = _split_frame(lib, s, cuda, 0, 0)
+    assert flags == 0 and torch.equal(img, ref)
+    _, _, flags, per_tile = _split_frame(lib, s, cuda, 0, 2)
+    assert flags & 2 and per_tile == 0
+    img, _, flags, per_tile = _split_frame(lib, s, cuda, 2, 2)
+    assert flags == 0 and per_tile == 1 and torch.equal(img, ref)
+    with pytest.raises(_lib.GGDError):
+        _split_frame(lib, s, cuda, 3, 1)
