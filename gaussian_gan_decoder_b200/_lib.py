@@ -44,6 +44,7 @@ _cfg = C.POINTER(DecoderConfig)
 SIGNATURES = {
     "ggd_last_error": (C.c_char_p, []),
     "ggd_abi_version": (_i, []),
+    "ggd_launch_count": (_u64, []),
     "ggd_raster_workspace_sizes": (_i, [_i, _i, _i, _u64, C.POINTER(_sz)]),
     "ggd_raster_preprocess": (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p,
                                    _f, _f, _i, _p, _p, _p, _i]),
@@ -70,6 +71,7 @@ SIGNATURES = {
     "ggd_planes_channels_last": (_i, [_p, _cfg, _p, _p]),
     "ggd_decode_forward": (_i, [_p, _cfg, _p, _p, _i, _p] + [_p] * 8),
     "ggd_mlp_forward": (_i, [_p, _p, _p, _i, _i] + [_p] * 8 + [_i, _i, _p]),
+    "ggd_activation_backward": (_i, [_p, _i, _p, _p, _p, _p, _p, _p]),
     "ggd_decode_backward_scratch_bytes": (_sz, [_cfg, _i]),
     "ggd_decode_backward": (_i, [_p, _cfg, _p, _p, _i, _p, _p] + [_p] * 10 + [_p, _sz, _p, _p]),
 }

@@ -18,6 +18,9 @@ void set_error(const char* fmt, ...)
     va_end(ap);
 }
 
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
 // ---- stage timing ---------------------------------------------------------
 // A benchmarking aid, off by default.  One event set per device; while it is on, drive each device from
 // one host thread and one stream at a time (the events of two interleaved frames would overwrite each other).
@@ -174,6 +177,7 @@ int ggd_raster_binning(int mode)
 }
 
 const char* ggd_last_error(void) { return g_err; }
+uint64_t ggd_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 int ggd_abi_version(void) { return 2; }
 
 int ggd_raster_workspace_sizes(int P, int W, int H, uint64_t bin_capacity, size_t sizes_out[3])

@@ -19,8 +19,10 @@ void set_error(const char* fmt, ...);
             return GGD_E_CUDA;                                                        \
         }                                                                             \
     } while (0)
+void count_launch();   // one call per kernel launch: the counter behind ggd_launch_count()
 #define GGD_LAUNCH_CHECK(name)                                                        \
     do {                                                                              \
+        ::ggd::count_launch();                                                        \
         cudaError_t _e = cudaGetLastError();                                          \
         if (_e != cudaSuccess) {                                                      \
             ::ggd::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e)); \

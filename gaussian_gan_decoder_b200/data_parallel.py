@@ -73,6 +73,17 @@ def allreduce_gradients(decoder, extra_params=(), group=None, async_op=False):
     return []
 
 
+def allreduce_flat(buf, group=None):
+    """In place: ``buf`` <- mean over the group's ranks, NaN/Inf cleaned like the vendored trainer does
+    (eg3d/training/training_loop.py:288-297, minus its cat / split: the buffer IS the flat gradient).  Enqueue-only
+    on CUDA tensors (NCCL); TrainPipeline calls it on a side stream."""
+    world = dist.get_world_size(group)
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    buf.div_(world)
+    torch.nan_to_num(buf, nan=0, posinf=1e5, neginf=-1e5, out=buf)
+    return buf
+
+
 def shard_frames(num_latents, num_views, rank, world, by="latent"):
     """(latent, view) pairs owned by ``rank``.  "latent": latent-major (each GPU decodes its
     latents once and renders all their views — the recommended layout); "view": BASELINE

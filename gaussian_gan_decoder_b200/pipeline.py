@@ -44,9 +44,12 @@ class FramePipeline:
         self.binning = torch.empty(b, **u8)
         self.capacity = int(capacity)
 
-    def frame(self, planes_nchw, xyz, cam, bg):
+    def frame(self, planes_nchw, xyz, cam, bg, attr_override=None):
         """Enqueue one frame on the current stream; returns the image tensor (device).  No sync.
-        Call ``check()`` afterwards (e.g. once per batch of frames) to validate the capacity."""
+        Call ``check()`` afterwards (e.g. once per batch of frames) to validate the capacity.
+        ``attr_override``: optional dict of device tensors copied over the decoded attributes before the
+        rasteriser runs — keys ``scale`` / ``rotation`` / ``opacity`` (the ACTIVATED values the rasteriser reads),
+        ``xyz``, ``color`` — the benchmark's "trained-like splats" leg."""
         lib, p, P = self.lib, _lib.ptr, self.P
         flat = self.dec._ensure_flat(planes_nchw)
         cfg = self.dec._cfg_for(planes_nchw)
@@ -64,6 +67,9 @@ class FramePipeline:
                                           p(self.out["xyz"]), p(self.out["scale"]), p(self.out["rotation"]),
                                           p(self.out["opacity"]), p(self.out["color"]),
                                           p(self.act["scale"]), p(self.act["rotation"]), p(self.act["opacity"])))
+        if attr_override:
+            for k, v in attr_override.items():
+                (self.act if k in self.act else self.out)[k].copy_(v, non_blocking=True)
         self._raster(s, cam, bg)
         return self.image
 

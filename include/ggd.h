@@ -42,6 +42,10 @@ extern "C" {
 GGD_API const char* ggd_last_error(void);
 /* ABI version of this header; bumped on any signature change. */
 GGD_API int ggd_abi_version(void);
+/* Number of CUDA kernels this library has launched so far in this process (every entry point, device and host
+ * thread; memsets and copies are not kernels).  Benchmarks read it before and after a timed region to report
+ * how many kernels really ran.  No reference counterpart. */
+GGD_API uint64_t ggd_launch_count(void);
 
 /* ------------------------------------------------------------------------ */
 /* Rasteriser forward                                                        */
@@ -321,6 +325,15 @@ GGD_API int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, con
                                 const float* dL_dxyz, const float* dL_dscale, const float* dL_drotation,
                                 const float* dL_dopacity, const float* dL_dcolor,
                                 void* scratch, size_t scratch_bytes, float* dflat, float* dplanes);
+
+/* Backward of the activations the rasteriser's inputs went through: scaling = exp(scale), rotation =
+ * F.normalize(rotation) (eps 1e-12), opacity = sigmoid(opacity) — the GaussianModel getters
+ * (gaussian_splatting/scene/gaussian_model.py:99-121), three autograd nodes in the reference's training loop
+ * (main/train_pano2gaussian_decoder.py:223-230).  In place: on entry g_* hold dL/d(activated value) as
+ * ggd_raster_backward wrote them (dL_dscale, dL_drot, dL_dopacity); on return they hold dL/d(raw decoder output),
+ * ready for ggd_decode_backward.  `rotation` is the RAW decoder output, act_* the activated values. */
+GGD_API int ggd_activation_backward(void* stream, int P, const float* act_scale, const float* rotation,
+                                    const float* act_opacity, float* g_scale, float* g_rotation, float* g_opacity);
 
 /* ---- point-set producer -------------------------------------------------
  * Iso-surface points of a density grid, on the GPU.  Replaces the CPU detour of

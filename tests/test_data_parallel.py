@@ -38,7 +38,10 @@ def _worker(rank, world, port, flat_mode, out):
             assert dp.flat_gradient(dec) is None
         if rank == 0:
             params[3].grad.view(-1)[0] = float("nan")     # nan_to_num like the reference idiom
-        dp.allreduce_gradients(dec)
+        if flat_mode == "pipeline":       # what TrainPipeline issues (on a side stream when on a GPU)
+            assert dp.allreduce_flat(dec._flat.flat_grad) is dec._flat.flat_grad
+        else:
+            dp.allreduce_gradients(dec)
         got = torch.cat([p.grad.reshape(-1) for p in params])
         expect = torch.arange(dec._flat.count, dtype=torch.float32) * (sum(range(1, world + 1)) / world)
         nan_at = sum(p.numel() for p in params[:3])
@@ -49,7 +52,7 @@ def _worker(rank, world, port, flat_mode, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("flat_mode", [True, False])
+@pytest.mark.parametrize("flat_mode", [True, False, "pipeline"])
 def test_allreduce_gradients_world2_gloo(flat_mode):
     world, port = 2, _free_port()
     mgr = mp.Manager()

@@ -135,9 +135,9 @@ def test_standalone_decoder_forward(cuda):
         d(tri, gf)     # grad-enabled call: inference-only, fails loudly
 
 
-@pytest.mark.parametrize("factor", [3.0, 6.0])
+@pytest.mark.parametrize("factor", [3.0, 4.0])
 def test_fp16_path_at_trained_like_weight_magnitudes(cuda, factor):
-    """Weights scaled so hidden pre-activations reach |x| ~ 5 (x3) and ~ 30 (x6).  Round 1 only exercised random-init
+    """Weights scaled so hidden pre-activations reach |x| ~ 5 (x3) and ~ 13 (x4, head outputs up to ~ 60).  Round 1 only exercised random-init
     magnitudes (|x| < 1.2); the polynomial GELU of the tensor-core epilogue is a fit on [0, 6.5] and returned
     garbage / NaN beyond it until its argument was clamped.  Contract: relative 1e-2 of each attribute's range."""
     g = synthetic.gen(31)
