@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libggd_b200.so")
 
 GGD_OK, GGD_E_INVALID, GGD_E_CUDA, GGD_E_CAPACITY = 0, 1, 2, 3
 ABI_VERSION = 2          # ggd_abi_version() of the library these signatures describe
-BINNING_RADIX, BINNING_AUTO, BINNING_TILES = 0, 1, 2
+BINNING_RADIX, BINNING_AUTO, BINNING_TILES, BINNING_LEAN = 0, 1, 2, 4
 
 
 class GGDError(RuntimeError):
@@ -70,6 +70,7 @@ SIGNATURES = {
     "ggd_decode_pack_weights": (_i, [_p, _cfg, _p, _p]),
     "ggd_planes_channels_last": (_i, [_p, _cfg, _p, _p]),
     "ggd_decode_forward": (_i, [_p, _cfg, _p, _p, _i, _p] + [_p] * 8),
+    "ggd_debug_decode_profile": (_i, [C.POINTER(C.c_uint64)]),
     "ggd_mlp_forward": (_i, [_p, _p, _p, _i, _i] + [_p] * 8 + [_i, _i, _p]),
     "ggd_activation_backward": (_i, [_p, _i, _p, _p, _p, _p, _p, _p]),
     "ggd_decode_backward_scratch_bytes": (_sz, [_cfg, _i]),

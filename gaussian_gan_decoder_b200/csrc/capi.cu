@@ -142,10 +142,14 @@ int default_binning()
     }
     return m;
 }
-bool resolve_binning(int& mode, const char* who)
+// `lean` (GGD_BINNING_LEAN or-ed into the mode): the per-tile path does not write the reference-order key/value arrays
+bool resolve_binning(int& mode, const char* who, bool* lean = nullptr)
 {
     if (mode == -1) mode = default_binning();
-    if (mode < 0 || mode > 2) { set_error("%s: binning must be -1 (default), 0, 1 or 2 (got %d)", who, mode); return false; }
+    const bool l = mode >= 0 && (mode & GGD_BINNING_LEAN) != 0;
+    if (mode >= 0) mode &= ~GGD_BINNING_LEAN;
+    if (lean) *lean = l;
+    if (mode < 0 || mode > 2) { set_error("%s: binning must be -1 (default), 0, 1 or 2, optionally | GGD_BINNING_LEAN (got %d)", who, mode); return false; }
     return true;
 }
 
@@ -241,7 +245,8 @@ int ggd_raster_render(void* stream, int P, int W, int H, const float* background
                       float* out_color, int binning)
 {
     if (int e = check_common(P, W, H)) return e;
-    if (!resolve_binning(binning, "ggd_raster_render")) return GGD_E_INVALID;
+    bool lean = false;
+    if (!resolve_binning(binning, "ggd_raster_render", &lean)) return GGD_E_INVALID;
     if (!background || !geom_ws || !bin_ws || !img_ws || !out_color) { set_error("ggd_raster_render: null required pointer"); return GGD_E_INVALID; }
     if (!aligned256(geom_ws) || !aligned256(bin_ws) || !aligned256(img_ws)) { set_error("state buffers must be 256-byte aligned"); return GGD_E_INVALID; }
     if (bin_capacity >= (1ull << 30)) { set_error("bin_capacity %llu exceeds 2^30-1", (unsigned long long)bin_capacity); return GGD_E_INVALID; }
@@ -265,7 +270,7 @@ int ggd_raster_render(void* stream, int P, int W, int H, const float* background
         StageScope t(s, kStDuplicate);
         if (per_tile) {   // writes every range, picks the path for this frame (counters[4])
             if (int e = launch_tile_scan(s, g, im, tiles, bin_capacity, P, !radix)) return e;
-            if (int e = launch_tile_scatter(s, P, grid_x, grid_y, g, radii, b, im, bin_capacity)) return e;
+            if (int e = launch_tile_scatter(s, P, grid_x, grid_y, g, radii, b, im, bin_capacity, !lean)) return e;
         } else {
             GGD_CUDA_CHECK(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)tiles, s));
         }
@@ -292,7 +297,7 @@ int ggd_raster_forward(void* stream, int P, int D, int M, const float* backgroun
                        void* geom_ws, void* bin_ws, uint64_t bin_capacity, void* img_ws,
                        float* out_color, int* radii, uint32_t* num_rendered_host, int binning)
 {
-    if (!resolve_binning(binning, "ggd_raster_forward")) return GGD_E_INVALID;
+    { int check = binning; if (!resolve_binning(check, "ggd_raster_forward")) return GGD_E_INVALID; }   // both stages resolve it again
     if (int e = ggd_raster_preprocess(stream, P, D, M, W, H, means3D, shs, colors_precomp, opacities,
                                       scales, scale_modifier, rotations, cov3D_precomp, viewmatrix,
                                       projmatrix, campos, tan_fovx, tan_fovy, prefiltered, geom_ws,

@@ -9,7 +9,14 @@ int launch_planes_channels_last(cudaStream_t s, const float* src, void* dst, int
 #include "decode_args.cuh"
 #include "decode_bwd.cuh"
 
+namespace ggd { int debug_decode_profile(unsigned long long out[12]); }
 using namespace ggd;
+
+extern "C" int ggd_debug_decode_profile(uint64_t out[12])
+{
+    if (!out) { set_error("ggd_debug_decode_profile: null pointer"); return GGD_E_INVALID; }
+    return debug_decode_profile(reinterpret_cast<unsigned long long*>(out));
+}
 
 namespace {
 int check_cfg(const ggd_decoder_config* c, DecoderLayout* L)

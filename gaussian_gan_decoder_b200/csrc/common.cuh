@@ -153,7 +153,7 @@ constexpr uint32_t kTileSortMax = 4096;   // longest tile list the register-resi
 constexpr uint32_t kTileSortLargeMax = 24576;   // longest list of the one-CTA-per-SM variant (192 KB of words + 32 KB of buckets)
 int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int tiles, uint64_t capacity, int P, bool strict);
 int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g, const int* radii,
-                        const BinState& b, const ImgState& im, uint64_t capacity);
+                        const BinState& b, const ImgState& im, uint64_t capacity, bool ref_order_arrays);
 int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, const ImgState& im, int tiles);
 int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const GeomState& g,
                  const BinState& b, const ImgState& im, const float* features,

@@ -81,9 +81,8 @@ decode_bwd_dw_mn_kernel(const DecoderLayout L, const uint8_t* __restrict__ stage
                     const uint32_t a_addr = sbase + sidx * kStageBytes, b_addr = a_addr + kABytes;
                     // MN-major, no swizzle: leading offset = stride between 8-point (K) blocks, stride offset = 128 B
                     // between 8-feature (M/N) blocks; one K=16 step advances two K blocks
-                    for (int s = 0; s < kTilePts / 16; ++s)
-                        ptx::mma_f16_ss(tmem_base, ptx::smem_desc(a_addr + s * 2 * 2048, 2048, 128),
-                                        ptx::smem_desc(b_addr + s * 2 * b_lbo, b_lbo, 128), idesc, (j > 0 || s > 0) ? 1u : 0u);
+                    ptx::mma_f16_ss_steps<kTilePts / 16>(tmem_base, ptx::smem_desc(a_addr, 2048, 128), ptx::smem_desc(b_addr, b_lbo, 128),
+                                                         2 * 2048 / 16, 2 * b_lbo / 16, idesc, j > 0);
                     ptx::mma_commit(&empty[sidx]);
                 }
                 ptx::mma_commit(done);

@@ -6,11 +6,12 @@
             const uint32_t id128 = ptx::idesc_f16(kM, 128), id16 = ptx::idesc_f16(kM, 16), id48 = ptx::idesc_f16(kM, kK0);
             const uint32_t id_dw3 = ptx::idesc_f16(128, 16) | (1u << 15) | (1u << 16);   // both operands MN-major (K = points)
             uint32_t cnt = 0, n_ready = 0;
-            auto mma_k = [&](uint32_t d, uint32_t a_addr, uint32_t a_K, uint32_t b_addr, uint32_t b_K, uint32_t idesc, int ksteps, bool acc0) {
-                for (int s = 0; s < ksteps; ++s)
-                    ptx::mma_f16_ss(d, ptx::smem_desc(a_addr + s * 256, 128, a_K * 16), ptx::smem_desc(b_addr + s * 256, 128, b_K * 16),
-                                    idesc, (acc0 || s > 0) ? 1u : 0u);
+            // descriptors built once per call, K steps unrolled at compile time (ptx::mma_f16_ss_steps)
+            auto mma_k = [&](uint32_t d, uint32_t a_addr, uint32_t a_K, uint32_t b_addr, uint32_t b_K, uint32_t idesc, auto ksteps, bool acc0) {
+                ptx::mma_f16_ss_steps<decltype(ksteps)::value>(d, ptx::smem_desc(a_addr, 128, a_K * 16), ptx::smem_desc(b_addr, 128, b_K * 16),
+                                                                16, 16, idesc, acc0);
             };
+            using std::integral_constant;
             for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
                 for (int hi = kHeads - 1; hi >= 0; --hi) {
                     const int h = L.order[hi];
@@ -28,20 +29,19 @@
                         if (stored) bulk_commit();
                         const uint32_t dacc = tmem_base + kColAcc;
                         switch (s) {
-                            case 0: mma_k(dacc, sb + kOffX0, kK0, w_addr, kK0, id128, kK0 / 16, false); break;
-                            case 1: case 2: mma_k(dacc, sb + kOffA, kKH, w_addr, kKH, id128, kKH / 16, false); break;
-                            case 3: mma_k(tmem_base + kColY, sb + kOffA, kKH, w_addr, kKH, id16, kKH / 16, false); break;
+                            case 0: mma_k(dacc, sb + kOffX0, kK0, w_addr, kK0, id128, integral_constant<int, kK0 / 16>{}, false); break;
+                            case 1: case 2: mma_k(dacc, sb + kOffA, kKH, w_addr, kKH, id128, integral_constant<int, kKH / 16>{}, false); break;
+                            case 3: mma_k(tmem_base + kColY, sb + kOffA, kKH, w_addr, kKH, id16, integral_constant<int, kKH / 16>{}, false); break;
                             case 4:
-                                mma_k(dacc, sb + kOffDY, 16, w_addr, 16, id128, 1, false);
+                                mma_k(dacc, sb + kOffDY, 16, w_addr, 16, id128, integral_constant<int, 1>{}, false);
                                 // dW3[k][j] += sum over the tile's points H3[p][k] dY[p][j]: H3 is still in the hidden operand
                                 // buffer ([point][unit], 144 columns), dY is [point][16]; contraction over the strided index
-                                for (int s2 = 0; s2 < kM / 16; ++s2)
-                                    ptx::mma_f16_ss(tmem_base + col_dw3(hi), ptx::smem_desc(sb + kOffA + s2 * 2 * (kKH * 16), kKH * 16, 128),
-                                                    ptx::smem_desc(sb + kOffDY + s2 * 2 * 256, 256, 128), id_dw3,
-                                                    (tile != (int)blockIdx.x || s2 > 0) ? 1u : 0u);
+                                ptx::mma_f16_ss_steps<kM / 16>(tmem_base + col_dw3(hi), ptx::smem_desc(sb + kOffA, kKH * 16, 128),
+                                                               ptx::smem_desc(sb + kOffDY, 256, 128), 2 * (kKH * 16) / 16, 2 * 256 / 16, id_dw3,
+                                                               tile != (int)blockIdx.x);
                                 break;
-                            case 5: case 6: mma_k(dacc, sb + kOffDZ, kHidden, w_addr, kHidden, id128, kHidden / 16, false); break;
-                            default: mma_k(tmem_base + kColDX, sb + kOffDZ, kHidden, w_addr, kHidden, id48, kHidden / 16, hi != kHeads - 1); break;
+                            case 5: case 6: mma_k(dacc, sb + kOffDZ, kHidden, w_addr, kHidden, id128, integral_constant<int, kHidden / 16>{}, false); break;
+                            default: mma_k(tmem_base + kColDX, sb + kOffDZ, kHidden, w_addr, kHidden, id48, integral_constant<int, kHidden / 16>{}, hi != kHeads - 1); break;
                         }
                         if (stored) bulk_wait_read();
                         ptx::mma_commit(&bars[B_ACC]);

@@ -90,28 +90,26 @@ __device__ __forceinline__ __half2 gelu_h2(__half2 x)
     return __hfma2(hx, th, hx);
 }
 // Same function without the MUFU pipe: gelu(x) = relu(x) - |x| * Phi(-|x|), with
-//   Phi(-a) = 0.5 erfc(a / sqrt 2) ~= relu(s + a (k1 + a (k2 + a k3)))^8,   s = 2^(-1/8)
-// (cubic fitted to erfc, max abs error of the resulting GELU 2.7e-4; every intermediate lies in [0, 1], so the
-// half2 evaluation is well conditioned: simulated rms error 3.4e-4 against 2.8e-4 for the tanh form).
-// Measured on B200 (scratch microbenchmark, warp-instructions per clock per SM sub-partition): HFMA2/HMUL2 0.5,
-// MUFU 0.125, so the tanh form costs 16 MUFU clocks + 10 FMA-pipe clocks per half2 and this form 14 FMA-pipe
-// clocks.  kMask selects the form per half2 of a thread's row segment (bit set = this form).
-constexpr float kPolyS = 0.917004043f, kPolyK1 = -0.09717107f * kPolyS, kPolyK2 = -0.04195465f * kPolyS,
-                kPolyK3 = 0.00527501f * kPolyS, kPolyClamp = 6.0f;
+//   Phi(-a) = 0.5 erfc(a / sqrt 2) ~= relu(q(a))^2,   q = quartic fitted (minimax on a * error) over [0, 6]
+// Max abs error of the resulting GELU 2.8e-4; evaluated in half2 (Horner) the simulated rms error against the exact
+// erf-GELU is 3.3e-4, the same as the tanh form's.  Six FMA-pipe instructions per half2 (4 HFMA2 + HMUL2 + HFMA2; round 1
+// shipped relu(cubic)^8 = seven) plus one HMNMX2 on the ALU pipe for the clamp.  Measured on B200 (profiles/ubench_pipes.cu):
+// HFMA2/HMUL2 issue every 2 clocks per SM sub-partition, MUFU every 8, so the tanh form costs 16 MUFU + 10 FMA-pipe
+// clocks per half2 and this form 12 FMA-pipe clocks.  kMask selects the form per half2 of a thread's row segment.
+constexpr float kPolyQ0 = 0.705270226f, kPolyQ1 = -0.274018594f, kPolyQ2 = -0.0765701305f, kPolyQ3 = 0.0498421696f,
+                kPolyQ4 = -0.00619701014f, kPolyClamp = 6.0f;
 __device__ __forceinline__ __half2 gelu_poly_h2(__half2 x)
 {
-    const __half2 k0 = __float2half2_rn(kPolyS), k1 = __float2half2_rn(kPolyK1), k2 = __float2half2_rn(kPolyK2),
-                  k3 = __float2half2_rn(kPolyK3), zero = __float2half2_rn(0.f);
-    // The cubic is a fit on [0, 6.5] and turns upward beyond it (at |x| = 10 it is back above 1, and its 8th
-    // power overflows soon after): clamp the argument where Phi(-a) has long vanished (6 * Phi(-6) = 6e-9; the
-    // fit's own residue there is below its 2.7e-4 bound), so gelu(x) = relu(x) - O(1e-4) for every |x| > 6.
-    // One min on the ALU pipe per half2; the FMA pipe, which bounds this epilogue, sees no extra work.
+    const __half2 q0 = __float2half2_rn(kPolyQ0), q1 = __float2half2_rn(kPolyQ1), q2 = __float2half2_rn(kPolyQ2),
+                  q3 = __float2half2_rn(kPolyQ3), q4 = __float2half2_rn(kPolyQ4), zero = __float2half2_rn(0.f);
+    // The fit holds on [0, 6] and the quartic leaves [0, 1] beyond it (round 1's cubic did too: at |x| ~ 10 its 8th
+    // power overflowed and the fp16 path returned NaN for trained-like weights).  Clamp the argument where Phi(-a)
+    // has long vanished (6 * Phi(-6) = 6e-9): gelu(x) = relu(x) - O(1e-4) for every |x| > 6.
     const __half2 ax = __hmin2(__habs2(x), __float2half2_rn(kPolyClamp));
-    __half2 p = __hfma2(ax, k3, k2);
-    p = __hfma2(p, ax, k1);
-    p = __hfma2_relu(p, ax, k0);
-    p = __hmul2(p, p);
-    p = __hmul2(p, p);
+    __half2 p = __hfma2(ax, q4, q3);
+    p = __hfma2(p, ax, q2);
+    p = __hfma2(p, ax, q1);
+    p = __hfma2_relu(p, ax, q0);
     p = __hmul2(p, p);
     return __hfma2(__hneg2(ax), p, __hmax2(x, zero));
 }

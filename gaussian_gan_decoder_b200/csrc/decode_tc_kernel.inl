@@ -34,10 +34,18 @@ __device__ __forceinline__ void gelu_block(const uint32_t* v, uint32_t* o)
     o[4 * J + 3] = *reinterpret_cast<const uint32_t*>(&y3);
 }
 
-template <uint32_t kMask>
+// Cycle accounting of one CTA's roles (GGD_DECODE_PROF=1 selects the instrumented instantiation; read back with
+// ggd_debug_decode_profile): [0] kernel, [1] epilogue warp 0 sampling, [2] waiting for an accumulator, [3] hidden-layer
+// epilogues, [4] last-layer epilogues, [5] MMA thread waiting for an operand, [6] for weights, [7] issuing.
+__device__ unsigned long long g_tc_prof[12];   // [8], [9]: MMA issue time of the layer-0 / last-layer steps (part of [7])
+
+template <uint32_t kMask, bool kProf = false>
 __global__ void __launch_bounds__(kTcThreads, 1)
 decode_tc_kernel(const DecodeFwdArgs a, const int T)
 {
+    long long pc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    auto now = [&]() -> long long { return kProf ? clock64() : 0ll; };
+    const long long t_kernel = now();
     extern __shared__ __align__(1024) uint8_t smem[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 128);
@@ -78,6 +86,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
         const size_t plane_stride = (size_t)a.D * a.H * a.W * kFeat;
         uint32_t n_acc[2] = {0, 0};
         for (int g = blockIdx.x; g < groups; g += gridDim.x) {
+            const long long t_s = now();
             // ---- sample all T tiles into their layer-0 operands: 4 lanes per point, 128 points per pass ----
             for (int i = 0; i < T; ++i) {
                 uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
@@ -145,6 +154,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                 ptx::mbar_arrive(&bars[B_AREADY]);
                 if (T > 1) ptx::mbar_arrive(&bars[B_AREADY + 1]);
             }
+            pc[1] += now() - t_s;
 
             int chain_col = kFeat + L.pos_dim;
             for (int hi = 0; hi < kHeads; ++hi) {
@@ -158,15 +168,16 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                             uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
                             const uint32_t trow = trow0 + (uint32_t)wg * kColSlot;
                             const int gp = (g * T + i) * kM + r;
-                            const bool post = (l == kLayers - 1) && colq == 0;   // this thread applies the head post-math
-                            float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
-                            if (post && h == kXyz && gp < a.P) {                 // issued ahead of the wait
-                                o0 = __ldg(a.xyz + 3 * (size_t)gp);
-                                o1 = __ldg(a.xyz + 3 * (size_t)gp + 1);
-                                o2 = __ldg(a.xyz + 3 * (size_t)gp + 2);
-                            }
+                            // last layer: the four warps of a lane quarter share the head's post-math, one output
+                            // component (colq) each — on one warp per quarter it took as long as a hidden-layer epilogue
+                            const bool post = (l == kLayers - 1) && colq < n_out;
+                            float xin = 0.f;
+                            if (post && h == kXyz && gp < a.P) xin = __ldg(a.xyz + 3 * (size_t)gp + colq);   // issued ahead of the wait
+                            const long long t_w = now();
                             if (lane == 0) ptx::mbar_wait_parked(&bars[B_ACCFULL + wg], n_acc[wg] & 1);   // one poller per warp
                             __syncwarp();
+                            const long long t_e = now();
+                            pc[2] += t_e - t_w;
                             ++n_acc[wg];
                             ptx::tc_fence_after();
                             if (l < kLayers - 1) {
@@ -187,38 +198,25 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                                 uint32_t v[4];
                                 ptx::tmem_ld4(trow + kColOut, v);
                                 ptx::tmem_ld_wait();
-                                const float y0 = __uint_as_float(v[0]), y1 = __uint_as_float(v[1]), y2 = __uint_as_float(v[2]);
-                                if (h == kXyz) {
-                                    o0 = y0 * 0.01f + o0; o1 = y1 * 0.01f + o1; o2 = y2 * 0.01f + o2;
-                                } else if (h == kScale) {
-                                    o0 = -softplus_f(y0 + 5.0f) + a.scale_bias;
-                                    o1 = -softplus_f(y1 + 5.0f) + a.scale_bias;
-                                    o2 = -softplus_f(y2 + 5.0f) + a.scale_bias;
-                                } else {
-                                    o0 = y0; o1 = y1; o2 = y2; o3 = __uint_as_float(v[3]);
-                                }
+                                const float y = __uint_as_float(colq == 0 ? v[0] : colq == 1 ? v[1] : colq == 2 ? v[2] : v[3]);
+                                float o;
+                                if (h == kXyz) o = y * 0.01f + xin;
+                                else if (h == kScale) o = -softplus_f(y + 5.0f) + a.scale_bias;
+                                else o = y;
                                 if (L.variant != 0 && hi < kHeads - 1) {
-                                    auto put = [&](int j, float val) {
-                                        if (j < n_out) *reinterpret_cast<__half*>(base + canon(r, chain_col + j, k0)) = __float2half_rn(val);
-                                    };
-                                    put(0, o0); put(1, o1); put(2, o2); put(3, o3);
+                                    *reinterpret_cast<__half*>(base + canon(r, chain_col + colq, k0)) = __float2half_rn(o);
                                     ptx::fence_proxy_async();
                                 }
-                            }
-                            if (post && gp < a.P) {
-                                float* dst = a.out[h] + (size_t)gp * n_out;
-                                dst[0] = o0;
-                                if (n_out > 1) { dst[1] = o1; dst[2] = o2; }
-                                if (n_out > 3) dst[3] = o3;
-                                if (h == kScale && a.act_scale) {
-                                    float* as = a.act_scale + (size_t)gp * 3;
-                                    as[0] = expf(o0); as[1] = expf(o1); as[2] = expf(o2);
-                                }
-                                if (h == kOpacity && a.act_opacity) a.act_opacity[gp] = 1.0f / (1.0f + expf(-o0));
-                                if (h == kRot && a.act_rot) {
-                                    const float inv = 1.0f / fmaxf(sqrtf(o0 * o0 + o1 * o1 + o2 * o2 + o3 * o3), 1e-12f);
-                                    float* ar = a.act_rot + (size_t)gp * 4;
-                                    ar[0] = o0 * inv; ar[1] = o1 * inv; ar[2] = o2 * inv; ar[3] = o3 * inv;
+                                if (gp < a.P) {
+                                    a.out[h][(size_t)gp * n_out + colq] = o;
+                                    if (h == kScale && a.act_scale) a.act_scale[(size_t)gp * 3 + colq] = expf(o);
+                                    if (h == kOpacity && a.act_opacity) a.act_opacity[gp] = 1.0f / (1.0f + expf(-o));
+                                    if (h == kRot && a.act_rot) {
+                                        const float y0 = __uint_as_float(v[0]), y1 = __uint_as_float(v[1]), y2 = __uint_as_float(v[2]),
+                                                    y3 = __uint_as_float(v[3]);
+                                        const float inv = 1.0f / fmaxf(sqrtf(y0 * y0 + y1 * y1 + y2 * y2 + y3 * y3), 1e-12f);
+                                        a.act_rot[(size_t)gp * 4 + colq] = o * inv;
+                                    }
                                 }
                             }
                             const bool last_of_group = (hi == kHeads - 1) && (i + 2 >= T) && (l == kLayers - 1);
@@ -227,6 +225,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                                 __syncwarp();
                                 if (lane == 0) ptx::mbar_arrive(&bars[B_AREADY + wg]);
                             }
+                            pc[l < kLayers - 1 ? 3 : 4] += now() - t_e;
                         }
                     }
                 }
@@ -243,11 +242,16 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                 for (int hi = 0; hi < kHeads; ++hi, ++n_head) {
                     for (int p = 0; p < (T + 1) / 2; ++p) {
                         for (int l = 0; l < kLayers; ++l) {
+                            const long long t_w0 = now();
                             if (p == 0) ptx::mbar_wait_parked(&bars[B_WFULL + l], n_head & 1);
+                            pc[6] += now() - t_w0;
                             for (int wg = 0; wg < 2; ++wg) {
                                 const int i = 2 * p + wg;
                                 if (i >= T) continue;
+                                const long long t_r = now();
                                 ptx::mbar_wait_parked(&bars[B_AREADY + wg], n_ready[wg] & 1);
+                                const long long t_i = now();
+                                pc[5] += t_i - t_r;
                                 ++n_ready[wg];
                                 ptx::tc_fence_after();
                                 const uint32_t b_addr = sbase + sm.w[l];
@@ -256,11 +260,15 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                                 const uint32_t idesc = l == kLayers - 1 ? id_out : id_hidden;
                                 const int K = l == 0 ? k0 : kKH;
                                 const uint32_t a_addr = sbase + (l == 0 ? sm.base0 + (uint32_t)i * sm.base_stride : sm.a[wg]);
-                                for (int s = 0; s < K / 16; ++s)
-                                    ptx::mma_f16_ss(d, ptx::smem_desc(a_addr + s * 256, 128, K * 16),
-                                                    ptx::smem_desc(b_addr + s * 256, 128, K * 16), idesc, s > 0 ? 1u : 0u);
+                                const uint64_t a_desc = ptx::smem_desc(a_addr, 128, K * 16), b_desc = ptx::smem_desc(b_addr, 128, K * 16);
+                                // descriptors built once per tile-layer, K steps unrolled (see mma_f16_ss_steps): a step of 16
+                                // columns is two core matrices = 256 bytes
+                                if (l != 0) ptx::mma_f16_ss_steps<kKH / 16>(d, a_desc, b_desc, 16, 16, idesc, false);
+                                else if (k0 == 48) ptx::mma_f16_ss_steps<3>(d, a_desc, b_desc, 16, 16, idesc, false);
+                                else ptx::mma_f16_ss_steps<7>(d, a_desc, b_desc, 16, 16, idesc, false);
                                 ptx::mma_commit(&bars[B_ACCFULL + wg]);
                                 if (i == T - 1) ptx::mma_commit(&bars[B_WEMPTY + l]);
+                                { const long long dt = now() - t_i; pc[7] += dt; if (l == 0) pc[8] += dt; if (l == kLayers - 1) pc[9] += dt; }
                             }
                         }
                     }
@@ -284,6 +292,10 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                 }
             }
         }
+    }
+    if (kProf && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 16)) {
+        pc[0] = now() - t_kernel;
+        for (int k = (warp == 0 ? 0 : 5); k < (warp == 0 ? 5 : 12); ++k) g_tc_prof[k] = (unsigned long long)pc[k];
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -309,9 +321,18 @@ int launch_decode_tc(cudaStream_t s, const DecodeFwdArgs& a, int num_sms)
     // GELU flavour of the hidden-layer epilogue: FMA-pipe form by default (measured 5 % faster than the MUFU
     // tanh form on B200, same accuracy); GGD_DECODE_GELU=tanh selects the other for comparison.
     const char* flavour = getenv("GGD_DECODE_GELU");
-    const int rc = (flavour && flavour[0] == 't') ? go(decode_tc_kernel<0x0000u>) : go(decode_tc_kernel<0xffffu>);
+    const char* prof = getenv("GGD_DECODE_PROF");
+    const int rc = (prof && prof[0] == '1') ? go(decode_tc_kernel<0xffffu, true>)
+                 : (flavour && flavour[0] == 't') ? go(decode_tc_kernel<0x0000u>) : go(decode_tc_kernel<0xffffu>);
     if (rc != GGD_OK) return rc;
     GGD_LAUNCH_CHECK("decode_tc_kernel");
+    return GGD_OK;
+}
+
+int debug_decode_profile(unsigned long long out[12])
+{
+    GGD_CUDA_CHECK(cudaDeviceSynchronize());
+    GGD_CUDA_CHECK(cudaMemcpyFromSymbol(out, g_tc_prof, sizeof(unsigned long long) * 12));
     return GGD_OK;
 }
 

@@ -78,6 +78,19 @@ __device__ __forceinline__ void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uin
     asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p; }"
                  ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// A K loop of kSteps MMAs from descriptors built ONCE: step s reads its operands a_step16 / b_step16 sixteen-byte
+// units further on (added to the descriptors' address fields; operands live below 256 KB, so no carry leaves the
+// field).  The issuer is one lane of one warp and runs at its dependent-issue latency; rebuilding the descriptors per
+// step cost 106 clocks per MMA on B200 against the 64 clocks a 128x128x16 MMA executes in (profiles/ubench_mma.cu).
+template <int kSteps>
+__device__ __forceinline__ void mma_f16_ss_steps(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t a_step16,
+                                                 uint32_t b_step16, uint32_t idesc, bool accumulate_first)
+{
+#pragma unroll
+    for (int s = 0; s < kSteps; ++s)
+        mma_f16_ss(d_tmem, a_desc + (uint64_t)(a_step16 * s), b_desc + (uint64_t)(b_step16 * s), idesc,
+                   (accumulate_first || s > 0) ? 1u : 0u);
+}
 // arrive on an mbarrier once every MMA issued so far by this thread has completed
 __device__ __forceinline__ void mma_commit(uint64_t* bar)
 {

@@ -107,6 +107,7 @@ constexpr int kScatterThreads = 256;
 // Same slot-centric walk as duplicate_kernel (binning.cu): CTA = 256 Gaussians' slot interval, thread =
 // slots s, s+256, ...; additionally to the reference-order key/value arrays (kept for the debug
 // accessors) every instance claims a place in its tile's segment.
+template <bool kRefOrder>
 __global__ void __launch_bounds__(kScatterThreads)
 tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ means2D,
                     const float* __restrict__ depths, const uint32_t* __restrict__ offsets,
@@ -155,8 +156,10 @@ tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ me
         const uint32_t rc = s_rect[g];
         const uint32_t tile = ((rc >> 16) + j / w) * (uint32_t)grid_x + (rc & 0xffffu) + j % w;
         const uint32_t depth = s_depth[g], id = (uint32_t)(base + g);
-        keys_unsorted[s] = ((uint64_t)tile << 32) | depth;
-        vals_unsorted[s] = id;
+        if (kRefOrder) {   // the reference's duplicateWithKeys output (emission order); nothing downstream reads it here
+            keys_unsorted[s] = ((uint64_t)tile << 32) | depth;
+            vals_unsorted[s] = id;
+        }
         const uint32_t pos = atomicAdd(cursors + (size_t)tile * kTileCountStride + 2, 1u);
         words[pos] = ((uint64_t)depth << 32) | id;
     }
@@ -405,6 +408,11 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ 
 constexpr int kLargeThreads = 1024;
 constexpr uint32_t kLargeBuckets = 8192;
 constexpr uint32_t kLargeInsertMax = 32;   // buckets up to this size are ordered by their owner thread
+// Lists up to this length are copied into the upper half of the CTA's shared memory first, so that the four passes
+// over the list (depth interval, coarse histogram, bucket histogram, distribution) read shared memory instead of
+// making four dependent round trips to L2 (the trained-like 512^2 frame: ~1000 lists of 5-10k words, 0.15 ms -> see
+// DESIGN.md); longer lists stream from global memory as before.
+constexpr uint32_t kLargeStagedMax = kTileSortLargeMax / 2;
 
 // ascending bitonic network on s[0..m) by the whole CTA ("normalised" form: every compare-exchange puts the
 // smaller word first, the first step of a phase mirrors, so positions >= m can be treated as +infinity)
@@ -449,9 +457,20 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         const uint64_t* src = words + range.x;
         // depth interval of the list
         uint32_t dmin = 0xffffffffu, dmax = 0u;
-        for (uint32_t i = t; i < n; i += kLargeThreads) {
-            const uint32_t d = (uint32_t)(__ldg(src + i) >> 32);
-            dmin = min(dmin, d); dmax = max(dmax, d);
+        if (n <= kLargeStagedMax) {
+            uint64_t* s_in = s_out + kLargeStagedMax;
+            for (uint32_t i = t; i < n; i += kLargeThreads) {
+                const uint64_t w = __ldg(src + i);
+                s_in[i] = w;
+                const uint32_t d = (uint32_t)(w >> 32);
+                dmin = min(dmin, d); dmax = max(dmax, d);
+            }
+            src = s_in;      // generic pointer into shared memory from here on (made visible by the barrier below)
+        } else {
+            for (uint32_t i = t; i < n; i += kLargeThreads) {
+                const uint32_t d = (uint32_t)(src[i] >> 32);
+                dmin = min(dmin, d); dmax = max(dmax, d);
+            }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -465,12 +484,12 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         __syncthreads();
         for (int k = 0; k < kLargeThreads / 32; ++k) { dmin = min(dmin, s_red[0][k]); dmax = max(dmax, s_red[1][k]); }
         BucketMap map{dmin, (float)kCoarse / ((float)(dmax - dmin) + 1.0f), (float)kLargeBuckets / (float)n, s_cstart, kLargeBuckets};
-        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_c[map.coarse((uint32_t)(__ldg(src + i) >> 32))], 1u);
+        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_c[map.coarse((uint32_t)(src[i] >> 32))], 1u);
         __syncthreads();
         coarse_scan(s_c, s_cstart);
         __syncthreads();
         auto bucket = [&](uint64_t w) { return map((uint32_t)(w >> 32)); };
-        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_hist[bucket(__ldg(src + i))], 1u);
+        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_hist[bucket(src[i])], 1u);
         __syncthreads();
         // exclusive scan; thread t owns buckets [t kPer, (t + 1) kPer)
         uint32_t cnt[kPer], sum = 0;
@@ -493,7 +512,7 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         }
         __syncthreads();
         for (uint32_t i = t; i < n; i += kLargeThreads) {
-            const uint64_t w = __ldg(src + i);
+            const uint64_t w = src[i];
             s_out[atomicAdd(&s_hist[bucket(w)], 1u)] = w;
         }
         __syncthreads();
@@ -543,13 +562,13 @@ int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int
 }
 
 int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g, const int* radii,
-                        const BinState& b, const ImgState& im, uint64_t capacity)
+                        const BinState& b, const ImgState& im, uint64_t capacity, bool ref_order_arrays)
 {
     (void)capacity; (void)im;
     const int blocks = (P + kScatterThreads - 1) / kScatterThreads;
-    tile_scatter_kernel<<<blocks, kScatterThreads, 0, s>>>(P, grid_x, grid_y, g.means2D, g.depths, g.point_offsets, radii,
-                                                           b.keys_unsorted, b.vals_unsorted, b.keys_tmp, g.tile_counts,
-                                                           g.counters);
+    auto kern = ref_order_arrays ? tile_scatter_kernel<true> : tile_scatter_kernel<false>;
+    kern<<<blocks, kScatterThreads, 0, s>>>(P, grid_x, grid_y, g.means2D, g.depths, g.point_offsets, radii,
+                                            b.keys_unsorted, b.vals_unsorted, b.keys_tmp, g.tile_counts, g.counters);
     GGD_LAUNCH_CHECK("tile_scatter_kernel");
     return GGD_OK;
 }

@@ -34,6 +34,8 @@ class FramePipeline:
         # cannot change it): starts at the library default; check() moves it to 2 (tiles only: no radix launches)
         # once a frame qualified, and back to 1 if one did not.
         self.bin_mode = self.lib.ggd_raster_binning(-1)
+        # a frame loop has no use for the reference-order key/value arrays (ggd.h: GGD_BINNING_LEAN); set False to keep them
+        self.lean = True
         self._alloc(capacity or 4 * P)
 
     def _alloc(self, capacity):
@@ -82,7 +84,7 @@ class FramePipeline:
             p(cam.world_view_transform), p(cam.full_proj_transform), p(cam.camera_center),
             math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), 0,
             p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
-            C.c_void_p(self.pinned.data_ptr()), self.bin_mode))
+            C.c_void_p(self.pinned.data_ptr()), self.bin_mode | (_lib.BINNING_LEAN if self.lean else 0)))
 
     def capture(self, planes_nchw, xyz, cam, bg):
         """Record one frame (planes -> decode -> rasterise) into a CUDA graph.  The graph reads the given

@@ -127,7 +127,7 @@ class TrainPipeline:
         check(lib.ggd_raster_forward(s, P, 0, 1, p(bg), self.W, self.H, p(o["xyz"]), p(o["color"]), None, p(a["opacity"]),
                                      p(a["scale"]), 1.0, p(a["rotation"]), None, p(view), p(proj), p(campos), tfx, tfy, 0,
                                      p(self.geom), p(self.binning), self.capacity, p(self.img), p(self.image), p(self.radii),
-                                     C.c_void_p(self.pinned.data_ptr()), self.bin_mode))
+                                     C.c_void_p(self.pinned.data_ptr()), self.bin_mode | self._lib.BINNING_LEAN))
         if dL_dimage is not None:
             dimg = dL_dimage
             self.loss.copy_((self.image * dL_dimage).sum())

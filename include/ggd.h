@@ -154,6 +154,10 @@ GGD_API int ggd_raster_status(void* stream, const void* geom_ws, int P, uint32_t
 #define GGD_BINNING_RADIX 0
 #define GGD_BINNING_AUTO 1
 #define GGD_BINNING_TILES 2
+/* Or-ed into a mode: a frame binned per tile does not write the reference-order arrays "point_list_keys_unsorted" /
+ * "point_list_unsorted" (duplicateWithKeys' output, 12 bytes per instance, read by nothing but ggd_raster_field
+ * users); sorted keys, point list, ranges and everything downstream are unchanged.  For frame loops. */
+#define GGD_BINNING_LEAN 4
 /* Sets the process DEFAULT used by calls that pass GGD_BINNING_DEFAULT; pass -1 to query.  Returns the
  * previous default. */
 GGD_API int ggd_raster_binning(int mode);
@@ -289,6 +293,14 @@ GGD_API int ggd_decode_forward(void* stream, const ggd_decoder_config* cfg, cons
                                float* out_xyz, float* out_scale, float* out_rotation,
                                float* out_opacity, float* out_color,
                                float* act_scale, float* act_rotation, float* act_opacity);
+
+/* Diagnostics: cycle accounting of the tcgen05 decoder's roles for CTA 0 of the last ggd_decode_forward launched with
+ * env GGD_DECODE_PROF=1 (an instrumented instantiation; the default build of the kernel carries no counters).
+ * out = { kernel, sampling, waiting for an accumulator, hidden-layer epilogues, last-layer epilogues (one epilogue
+ * warp); MMA thread: waiting for an operand, waiting for weights, issuing, of which layer-0 steps, last-layer steps;
+ * two spare words }.  Synchronises the device.
+ * No reference counterpart. */
+GGD_API int ggd_debug_decode_profile(uint64_t out[12]);
 
 /* One decoder head on caller-supplied features: mean over the three plane
  * samples, concat with gaussian_features, Linear-GELU x3, Linear.  Replaces

@@ -441,5 +441,9 @@ def test_binning_mode_mismatch_between_stages_is_safe(cuda):
     assert flags & 2 and per_tile == 0
     img, _, flags, per_tile = _split_frame(lib, s, cuda, 2, 2)
     assert flags == 0 and per_tile == 1 and torch.equal(img, ref)
+    # GGD_BINNING_LEAN: per-tile binning without the reference-order debug arrays — same image
+    for m in (1 | _lib.BINNING_LEAN, 2 | _lib.BINNING_LEAN, 0 | _lib.BINNING_LEAN):
+        img, _, flags, _ = _split_frame(lib, s, cuda, m, m)
+        assert flags == 0 and torch.equal(img, ref), m
     with pytest.raises(_lib.GGDError):
         _split_frame(lib, s, cuda, 3, 1)
