@@ -51,3 +51,20 @@ for r in rows[2:]:
         vals.append(v)
     out.append(f"| {name} | " + " | ".join(vals) + " |")
 print("\n".join(out))
+
+# The roofline object of bench.py reads the dominant kernel's DRAM traffic from here (never a literal in bench.py):
+# dram__bytes_read.sum + dram__bytes_write.sum of one decode_tc_kernel launch in THIS capture.
+import json
+import os
+units = rows[1]
+scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+for r in rows[2:]:
+    if "decode_tc_kernel" in r[h["Kernel Name"]]:
+        tot_b = sum(float(r[h[c]].replace(",", "")) * scale.get(units[h[c]], 1.0)
+                    for c in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+        head = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "roofline_traffic.json")
+        json.dump({"kernel": "decode_tc_kernel", "dram_bytes_per_launch": tot_b,
+                   "source": f"profiles/{tag}_summary.md: ncu --set full --clock-control none, one launch (cold caches, serialised)",
+                   "captured_at_head": head}, open(path, "w"), indent=1)
+        break

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """The benchmark's trained-like frame (500k Gaussians, 512^2, attributes overridden before the rasteriser) run a few
-times — a small target for ncu / per-stage timing.   python tools/trained_like_frame.py [frames]"""
+times — a small target for ncu / per-stage timing.   python tools/trained_like_frame.py [frames] [--random-init]"""
 import ctypes as C
 import os
 import sys
@@ -14,6 +14,7 @@ from gaussian_gan_decoder_b200 import _lib, synthetic  # noqa: E402
 from gaussian_gan_decoder_b200.pipeline import FramePipeline  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 6
+random_init = "--random-init" in sys.argv      # the headline frame: decoded attributes as they are
 dev = torch.device("cuda:0")
 lib = _lib.load()
 planes, xyz = [t.to(dev) for t in bench.make_inputs(0, dev, n_sets=1)[0]]
@@ -22,7 +23,7 @@ cam = bench.device_camera(dev)
 bg = torch.tensor(synthetic.BG[bench.ARCH], device=dev)
 tl = synthetic.trained_like_attributes(bench.P_FULL, synthetic.gen(77))
 act = synthetic.activated(tl)
-override = {"scale": act["scales"].to(dev), "rotation": act["rotations"].to(dev), "opacity": act["opacities"].to(dev),
+override = None if random_init else {"scale": act["scales"].to(dev), "rotation": act["rotations"].to(dev), "opacity": act["opacities"].to(dev),
             "color": tl["color"].to(dev)}
 pipe = FramePipeline(dec, bench.P_FULL, bench.SIZE, dev, capacity=16 * bench.P_FULL)
 for _ in range(3):
