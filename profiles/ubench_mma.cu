@@ -141,8 +141,60 @@ __global__ void __launch_bounds__(576, 1) k2(int iters, long long* out, int hamm
     if (warp == 0) ptx::tmem_dealloc<512>(tm);
 }
 
+// ---- one tile-layer at a time: 9 MMAs, commit, wait for completion — what a dependent step of the decoder costs ----
+template <int kSteps>
+__global__ void __launch_bounds__(256, 1) k3(int iters, long long* out, int N)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t slot;
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { ptx::mbar_init(&bar, 1); ptx::mbar_fence_init(); }
+    if (warp == 0) ptx::tmem_alloc<512>(&slot);
+    for (int i = threadIdx.x; i < 160 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+    ptx::fence_proxy_async();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tm = slot;
+    const uint32_t sa = ptx::smem_u32(smem), sb = sa + 64 * 1024;
+    const uint32_t idesc = ptx::idesc_f16(128, N);
+    const uint64_t a0 = desc(sa, 128, 16 * 16 * 9, 0), b0 = desc(sb, 128, 16 * 16 * 9, 0);
+    if (threadIdx.x == 0) {
+        long long t_issue = 0, t_total = 0;
+        for (int it = 0; it < iters; ++it) {
+            const long long t0 = clock64();
+#pragma unroll
+            for (int s = 0; s < kSteps; ++s) ptx::mma_f16_ss(tm, a0 + 16 * s, b0 + 16 * s, idesc, s ? 1u : 0u);
+            ptx::mma_commit(&bar);
+            const long long t1 = clock64();
+            ptx::mbar_wait(&bar, it & 1);
+            const long long t2 = clock64();
+            t_issue += t1 - t0; t_total += t2 - t0;
+        }
+        if (blockIdx.x == 0) { out[0] = t_issue; out[1] = t_total; }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) ptx::tmem_dealloc<512>(tm);
+}
+
 int main()
 {
+    {
+        long long* d; cudaMalloc(&d, 64);
+        long long h[2];
+        cudaFuncSetAttribute(k3<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(k3<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        for (int n : {128, 16}) {
+            k3<9><<<148, 256, 200 * 1024>>>(400, d, n);
+            if (cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("k3 failed\n"); return 1; }
+            printf("burst of 9 MMAs N=%3d + commit + wait: issue %.0f clk, until complete %.0f clk per burst\n", n, h[0] / 400.0, h[1] / 400.0);
+        }
+        k3<3><<<148, 256, 200 * 1024>>>(400, d, 128);
+        cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
+        printf("burst of 3 MMAs N=128 + commit + wait: issue %.0f clk, until complete %.0f clk per burst\n", h[0] / 400.0, h[1] / 400.0);
+    }
     {
         long long* d; cudaMalloc(&d, 64);
         long long h[2];
