@@ -1,4 +1,4 @@
-"""Generates tests/golden/decoder_snapshot.pkl (+ .pt, + expected flat parameters) with the REFERENCE's own classes and
+"""Generates tests/golden/snapshot_decoder.pkl (+ .pt, + expected flat parameters) with the REFERENCE's own classes and
 its own snapshot code path (main/train_pano2gaussian_decoder.py:297-307: pickle.dump of the persistent decoder object
 and torch.save of its state_dict).  Run in the build container:   python tests/golden/make_decoder_pickle.py
 The generator is a tiny stand-in (a real EG3D / PanoHead G is hundreds of MB and out of scope)."""
@@ -39,9 +39,9 @@ with torch.no_grad():
     for p in dec.parameters():
         p.copy_(p.half().float())          # fp16-representable: the expected values below store in 2 bytes each
 snapshot = dict(training_set_kwargs=dnnlib.EasyDict(lr=9e-5, num_iter=10), decoder=dec, dataloader=None)
-with open(os.path.join(HERE, "decoder_snapshot.pkl"), "wb") as f:
+with open(os.path.join(HERE, "snapshot_decoder.pkl"), "wb") as f:
     pickle.dump(snapshot, f)
-torch.save(dec.state_dict(), os.path.join(HERE, "decoder_snapshot.pt"))
+torch.save(dec.state_dict(), os.path.join(HERE, "snapshot_decoder.pt"))
 flat = torch.cat([p.detach().reshape(-1) for p in dec.get_params_custom()[:40]])
-np.savez_compressed(os.path.join(HERE, "decoder_snapshot_expected.npz"), flat_fp16=flat.half().numpy())
-print("wrote decoder_snapshot.{pkl,pt} and expected flat params", flat.numel())
+np.savez_compressed(os.path.join(HERE, "snapshot_decoder_expected.npz"), flat_fp16=flat.half().numpy())
+print("wrote snapshot_decoder.{pkl,pt} and expected flat params", flat.numel())

@@ -13,7 +13,7 @@ from gaussian_gan_decoder_b200.decoder_models import ParallelDecoder, Sequential
 from gaussian_gan_decoder_b200.decoder_utils import checkpoint
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-EXPECT = torch.from_numpy(np.load(os.path.join(GOLD, "decoder_snapshot_expected.npz"))["flat_fp16"].astype(np.float32))
+EXPECT = torch.from_numpy(np.load(os.path.join(GOLD, "snapshot_decoder_expected.npz"))["flat_fp16"].astype(np.float32))
 
 
 def _flat(dec):
@@ -27,7 +27,7 @@ def _G():
 def test_pickle_opens_without_the_reference_tree():
     for m in ("torch_utils", "dnnlib", "training"):
         assert m not in sys.modules or "reference" not in (getattr(sys.modules[m], "__file__", "") or "")
-    dec, info = checkpoint.load_decoder_pickle(os.path.join(GOLD, "decoder_snapshot.pkl"), _G(), device="cpu")
+    dec, info = checkpoint.load_decoder_pickle(os.path.join(GOLD, "snapshot_decoder.pkl"), _G(), device="cpu")
     assert isinstance(dec, SequentialDecoderReverse) and info["class_name"] == "SequentialDecoderReverse"
     assert info["init_kwargs"] == dict(hidden_dim=128, use_xyz_embedding=False, use_gen_finetune=True)
     assert torch.equal(_flat(dec), EXPECT)
@@ -42,11 +42,11 @@ def test_pickle_opens_without_the_reference_tree():
 
 def test_state_dict_file_loads_and_mismatches_fail_loudly():
     dec = SequentialDecoderReverse(_G(), use_xyz_embedding=False, use_gen_finetune=False, device="cpu")
-    rest = checkpoint.load_state_dict_file(dec, os.path.join(GOLD, "decoder_snapshot.pt"))
+    rest = checkpoint.load_state_dict_file(dec, os.path.join(GOLD, "snapshot_decoder.pt"))
     assert torch.equal(_flat(dec), EXPECT)
     assert list(rest) == ["G.w"]
     other = ParallelDecoder(_G(), use_xyz_embedding=False, use_gen_finetune=False, device="cpu")
     with pytest.raises((KeyError, RuntimeError)):          # chained heads have wider first layers: shapes differ
-        checkpoint.load_state_dict_file(other, os.path.join(GOLD, "decoder_snapshot.pt"))
+        checkpoint.load_state_dict_file(other, os.path.join(GOLD, "snapshot_decoder.pt"))
     with pytest.raises(KeyError):
         checkpoint.load_state_dict_file(dec, {"xyz_decoder.backbone.0.weight": torch.zeros(128, 46)})
