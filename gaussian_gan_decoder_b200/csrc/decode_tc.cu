@@ -31,10 +31,13 @@ namespace {
 constexpr int kM = 128;                       // points per tile == TMEM lanes
 constexpr int kKH = kHidden + 16;             // hidden-layer K incl. the bias column block
 constexpr int kNOut = 16;                     // last layer N (>= 4 outputs, MMA minimum for M=128)
-constexpr int kAStageBytes = kM * kKH * 2;    // 36864
+constexpr int kAStageBytes = kM * kHidden * 2;    // 32768: one hidden-layer A operand (the bias column block is shared, kOnesBytes)
+constexpr int kWHBytes = kHidden * kKH * 2;      // 36864: hidden-layer weights incl. the bias columns
+constexpr int kOnesBytes = kM * 16 * 2;          // 4096: [128 rows][16 columns] = 1, 0, .., 0 — the A operand of every bias step
+constexpr int kSlots = 3;                        // tiles in flight (operand stage + accumulator each)
 constexpr int kW3Bytes = kNOut * kKH * 2;     // 4608
 // tensor-memory columns of one slot: hidden accumulator | last-layer accumulator | fp16 activations (A operand)
-constexpr uint32_t kColOut = 128, kColA = 144, kColSlot = 256;
+constexpr uint32_t kColOut = 128, kColSlot = 160;   // 3 slots x 160 columns <= 512
 constexpr int kTcThreads = 576;             // 16 epilogue warps + MMA warp + loader warp
 constexpr float kGeluC0 = 0.8f, kGeluC1 = 0.0348f;   // tanh-form fit to erf-GELU, max abs err 2.9e-4
 
@@ -55,7 +58,7 @@ __host__ __device__ inline TcLayout tc_layout(int pos_dim)
     TcLayout t;
     t.k0 = pos_dim == 3 ? 48 : 112;
     t.bytes[0] = (size_t)kM * t.k0 * 2;
-    t.bytes[1] = t.bytes[2] = kAStageBytes;
+    t.bytes[1] = t.bytes[2] = kWHBytes;
     t.bytes[3] = kW3Bytes;
     t.off[0] = 0;
     for (int l = 1; l < kLayers; ++l) t.off[l] = t.off[l - 1] + t.bytes[l - 1];

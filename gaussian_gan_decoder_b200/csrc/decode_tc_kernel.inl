@@ -4,22 +4,22 @@ namespace {
 
 struct TcSmem {
     // byte offsets into dynamic shared memory
-    uint32_t w[kLayers], a[2], base0, base_stride, total;
+    uint32_t w[kLayers], a[kSlots], ones, base0, base_stride, total;
 };
 __host__ __device__ inline TcSmem tc_smem(const TcLayout& t, int T)
 {
     TcSmem s;
     uint32_t o = 256;   // barriers + tmem slot
     for (int l = 0; l < kLayers; ++l) { s.w[l] = o; o += (uint32_t)t.bytes[l]; }
-    s.a[0] = o; o += kAStageBytes;
-    s.a[1] = o; o += kAStageBytes;
+    for (int k = 0; k < kSlots; ++k) { s.a[k] = o; if (k < T) o += kAStageBytes; }   // a group of T < kSlots tiles uses T slots
+    s.ones = o; o += kOnesBytes;
     s.base0 = o; s.base_stride = (uint32_t)(kM * t.k0 * 2);
     o += s.base_stride * T;
     s.total = o;
     return s;
 }
 
-enum { B_WFULL = 0, B_WEMPTY = 4, B_AREADY = 8, B_ACCFULL = 10, B_COUNT = 12 };
+enum { B_WFULL = 0, B_WEMPTY = 4, B_AREADY = 8, B_ACCFULL = 8 + kSlots, B_COUNT = 8 + 2 * kSlots };
 
 // eight accumulator columns (four half2 pairs, block J of a thread's 32) -> activated fp16 operand
 template <uint32_t kMask, int J>
@@ -57,8 +57,10 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
 
     if (tid == 0) {
         for (int i = 0; i < 8; ++i) ptx::mbar_init(&bars[i], 1);
-        ptx::mbar_init(&bars[B_AREADY], 16); ptx::mbar_init(&bars[B_AREADY + 1], 16);   // one arrival per epilogue warp
-        ptx::mbar_init(&bars[B_ACCFULL], 1); ptx::mbar_init(&bars[B_ACCFULL + 1], 1);
+        for (int k = 0; k < kSlots; ++k) {
+            ptx::mbar_init(&bars[B_AREADY + k], 16);   // one arrival per epilogue warp
+            ptx::mbar_init(&bars[B_ACCFULL + k], 1);
+        }
         ptx::mbar_fence_init();
     }
     if (warp == 16) ptx::tmem_alloc<512>(tmem_slot);
@@ -76,15 +78,13 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
         // tile-layer epilogue is short; while they convert slot A the tensor core runs slot B's MMAs.
         const int e = tid, r = e & 127, colq = e >> 7;          // row (point) and 32-column block of this thread
         const uint32_t trow0 = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-        if (colq == 0) {   // constant bias-column block of both hidden operands: k = 128 is 1, k = 129..143 are 0
+        if (colq == 0) {   // the bias step's A operand, shared by every slot: column 0 is 1, columns 1..15 are 0
             const uint4 one = make_uint4(0x00003c00u, 0u, 0u, 0u), zero = make_uint4(0u, 0u, 0u, 0u);
-            for (int w2 = 0; w2 < 2; ++w2) {
-                *reinterpret_cast<uint4*>(smem + sm.a[w2] + canon(r, kHidden, kKH)) = one;
-                *reinterpret_cast<uint4*>(smem + sm.a[w2] + canon(r, kHidden + 8, kKH)) = zero;
-            }
+            *reinterpret_cast<uint4*>(smem + sm.ones + canon(r, 0, 16)) = one;
+            *reinterpret_cast<uint4*>(smem + sm.ones + canon(r, 8, 16)) = zero;
         }
         const size_t plane_stride = (size_t)a.D * a.H * a.W * kFeat;
-        uint32_t n_acc[2] = {0, 0};
+        uint32_t n_acc[kSlots] = {0, 0, 0};
         for (int g = blockIdx.x; g < groups; g += gridDim.x) {
             const long long t_s = now();
             // ---- sample all T tiles into their layer-0 operands: 4 lanes per point, 128 points per pass ----
@@ -150,20 +150,19 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
             ptx::fence_proxy_async();
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) {
-                ptx::mbar_arrive(&bars[B_AREADY]);
-                if (T > 1) ptx::mbar_arrive(&bars[B_AREADY + 1]);
-            }
+            if (lane == 0)
+                for (int k = 0; k < kSlots && k < T; ++k) ptx::mbar_arrive(&bars[B_AREADY + k]);
             pc[1] += now() - t_s;
 
             int chain_col = kFeat + L.pos_dim;
             for (int hi = 0; hi < kHeads; ++hi) {
                 const int h = L.order[hi];
                 const int n_out = head_out(h);
-                for (int p = 0; p < (T + 1) / 2; ++p) {
+                for (int p = 0; p < (T + kSlots - 1) / kSlots; ++p) {
                     for (int l = 0; l < kLayers; ++l) {
-                        for (int wg = 0; wg < 2; ++wg) {
-                            const int i = 2 * p + wg;
+#pragma unroll
+                        for (int wg = 0; wg < kSlots; ++wg) {
+                            const int i = kSlots * p + wg;
                             if (i >= T) continue;
                             uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
                             const uint32_t trow = trow0 + (uint32_t)wg * kColSlot;
@@ -189,7 +188,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                                 gelu_block<kMask, 1>(v, o);
                                 gelu_block<kMask, 2>(v, o);
                                 gelu_block<kMask, 3>(v, o);
-                                uint8_t* dstA = smem + sm.a[wg] + canon(r, colq * 32, kKH);
+                                uint8_t* dstA = smem + sm.a[wg] + canon(r, colq * 32, kHidden);
 #pragma unroll
                                 for (int j = 0; j < 4; ++j)
                                     *reinterpret_cast<uint4*>(dstA + 128 * j) = make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
@@ -219,7 +218,7 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                                     }
                                 }
                             }
-                            const bool last_of_group = (hi == kHeads - 1) && (i + 2 >= T) && (l == kLayers - 1);
+                            const bool last_of_group = (hi == kHeads - 1) && (i + kSlots >= T) && (l == kLayers - 1);
                             ptx::tc_fence_before();
                             if (!last_of_group) {
                                 __syncwarp();
@@ -235,18 +234,19 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
     } else if (warp == 16) {
         // ================================= MMA issuer =================================
         if (lane == 0) {
-            uint32_t n_ready[2] = {0, 0}, n_head = 0;
+            uint32_t n_ready[kSlots] = {0, 0, 0}, n_head = 0;
             const uint32_t id_hidden = ptx::idesc_f16(kM, kHidden), id_out = ptx::idesc_f16(kM, kNOut);
             const uint32_t sbase = ptx::smem_u32(smem);
             for (int g = blockIdx.x; g < groups; g += gridDim.x) {
                 for (int hi = 0; hi < kHeads; ++hi, ++n_head) {
-                    for (int p = 0; p < (T + 1) / 2; ++p) {
+                    for (int p = 0; p < (T + kSlots - 1) / kSlots; ++p) {
                         for (int l = 0; l < kLayers; ++l) {
                             const long long t_w0 = now();
                             if (p == 0) ptx::mbar_wait_parked(&bars[B_WFULL + l], n_head & 1);
                             pc[6] += now() - t_w0;
-                            for (int wg = 0; wg < 2; ++wg) {
-                                const int i = 2 * p + wg;
+#pragma unroll
+                            for (int wg = 0; wg < kSlots; ++wg) {
+                                const int i = kSlots * p + wg;
                                 if (i >= T) continue;
                                 const long long t_r = now();
                                 ptx::mbar_wait_parked(&bars[B_AREADY + wg], n_ready[wg] & 1);
@@ -258,14 +258,21 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
                                 const uint32_t tslot = tmem_base + (uint32_t)wg * kColSlot;
                                 const uint32_t d = tslot + (l == kLayers - 1 ? kColOut : 0);
                                 const uint32_t idesc = l == kLayers - 1 ? id_out : id_hidden;
-                                const int K = l == 0 ? k0 : kKH;
-                                const uint32_t a_addr = sbase + (l == 0 ? sm.base0 + (uint32_t)i * sm.base_stride : sm.a[wg]);
-                                const uint64_t a_desc = ptx::smem_desc(a_addr, 128, K * 16), b_desc = ptx::smem_desc(b_addr, 128, K * 16);
                                 // descriptors built once per tile-layer, K steps unrolled (see mma_f16_ss_steps): a step of 16
                                 // columns is two core matrices = 256 bytes
-                                if (l != 0) ptx::mma_f16_ss_steps<kKH / 16>(d, a_desc, b_desc, 16, 16, idesc, false);
-                                else if (k0 == 48) ptx::mma_f16_ss_steps<3>(d, a_desc, b_desc, 16, 16, idesc, false);
-                                else ptx::mma_f16_ss_steps<7>(d, a_desc, b_desc, 16, 16, idesc, false);
+                                if (l != 0) {
+                                    // 8 steps over the slot's 128 activation columns, then the bias step: A = the shared
+                                    // constant-one block, B = the weights' columns 128..143 (bias, zeros)
+                                    const uint64_t a_desc = ptx::smem_desc(sbase + sm.a[wg], 128, kHidden * 16);
+                                    const uint64_t b_desc = ptx::smem_desc(b_addr, 128, kKH * 16);
+                                    ptx::mma_f16_ss_steps<kHidden / 16>(d, a_desc, b_desc, 16, 16, idesc, false);
+                                    ptx::mma_f16_ss(d, ptx::smem_desc(sbase + sm.ones, 128, 16 * 16), b_desc + 16u * (kHidden / 16), idesc, 1u);
+                                } else {
+                                    const uint64_t a_desc = ptx::smem_desc(sbase + sm.base0 + (uint32_t)i * sm.base_stride, 128, k0 * 16);
+                                    const uint64_t b_desc = ptx::smem_desc(b_addr, 128, k0 * 16);
+                                    if (k0 == 48) ptx::mma_f16_ss_steps<3>(d, a_desc, b_desc, 16, 16, idesc, false);
+                                    else ptx::mma_f16_ss_steps<7>(d, a_desc, b_desc, 16, 16, idesc, false);
+                                }
                                 ptx::mma_commit(&bars[B_ACCFULL + wg]);
                                 if (i == T - 1) ptx::mma_commit(&bars[B_WEMPTY + l]);
                                 { const long long dt = now() - t_i; pc[7] += dt; if (l == 0) pc[8] += dt; if (l == kLayers - 1) pc[9] += dt; }
@@ -307,8 +314,8 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
 int launch_decode_tc(cudaStream_t s, const DecodeFwdArgs& a, int num_sms)
 {
     const TcLayout tl = tc_layout(a.L.pos_dim);
-    int T = 4;
-    while (T > 1 && tc_smem(tl, T).total > 227 * 1024) T >>= 1;
+    int T = kSlots;      // a group = one tile per slot; every weight load serves the whole group
+    while (T > 1 && tc_smem(tl, T).total > 227 * 1024) --T;
     const TcSmem sm = tc_smem(tl, T);
     if (sm.total > 227 * 1024) { set_error("decode_tc: shared memory budget exceeded (%u bytes)", sm.total); return GGD_E_INVALID; }
     const int groups = (a.P + kM * T - 1) / (kM * T);
