@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(576, 1) k2(int iters, long long* out, int hamm
 
 // ---- one tile-layer at a time: 9 MMAs, commit, wait for completion — what a dependent step of the decoder costs ----
 template <int kSteps>
-__global__ void __launch_bounds__(256, 1) k3(int iters, long long* out, int N)
+__global__ void __launch_bounds__(640, 1) k3(int iters, long long* out, int N, int ldtm_warps = 0, int f16acc = 0)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar;
@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(256, 1) k3(int iters, long long* out, int N)
     ptx::tc_fence_after();
     const uint32_t tm = slot;
     const uint32_t sa = ptx::smem_u32(smem), sb = sa + 64 * 1024;
-    const uint32_t idesc = ptx::idesc_f16(128, N);
+    const uint32_t idesc = f16acc ? (ptx::idesc_f16(128, N) & ~(3u << 4)) : ptx::idesc_f16(128, N);   // bits [4,6): 0 = f16 accumulator
     const uint64_t a0 = desc(sa, 128, 16 * 16 * 9, 0), b0 = desc(sb, 128, 16 * 16 * 9, 0);
     if (threadIdx.x == 0) {
         long long t_issue = 0, t_total = 0;
@@ -173,6 +173,28 @@ __global__ void __launch_bounds__(256, 1) k3(int iters, long long* out, int N)
             t_issue += t1 - t0; t_total += t2 - t0;
         }
         if (blockIdx.x == 0) { out[0] = t_issue; out[1] = t_total; }
+    } else if (warp >= 4 && warp < 4 + ldtm_warps) {
+        // epilogue-like tensor-memory reads of ANOTHER accumulator (columns 256..383) while the MMAs write columns 0..127
+        const uint32_t trow = tm + ((uint32_t)((warp & 3) * 32) << 16) + 256 + ((warp >> 2) & 3) * 32;
+        uint32_t acc = 0;
+        for (int it = 0; it < iters * 6; ++it) {
+            if (f16acc) {     // 32 columns of 16-bit accumulators packed two per register
+                uint32_t v[16];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                             : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+                               "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]) : "r"(trow) : "memory");
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int q = 0; q < 16; ++q) acc += v[q];
+            } else {
+                uint32_t v[32];
+                ptx::tmem_ld32(trow, v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc += v[q];
+            }
+        }
+        if (acc == 0x12345u) out[3] = acc;
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -190,6 +212,16 @@ int main()
             k3<9><<<148, 256, 200 * 1024>>>(400, d, n);
             if (cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("k3 failed\n"); return 1; }
             printf("burst of 9 MMAs N=%3d + commit + wait: issue %.0f clk, until complete %.0f clk per burst\n", n, h[0] / 400.0, h[1] / 400.0);
+        }
+        for (int lw : {4, 16}) {
+            k3<9><<<148, 640, 200 * 1024>>>(400, d, 128, lw);
+            if (cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("k3 ldtm failed\n"); return 1; }
+            printf("burst of 9 MMAs N=128 with %2d warps reading tensor memory: issue %.0f clk, until complete %.0f clk per burst\n", lw, h[0] / 400.0, h[1] / 400.0);
+        }
+        for (int lw : {0, 16}) {
+            k3<9><<<148, 640, 200 * 1024>>>(400, d, 128, lw, 1);
+            if (cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("k3 f16 failed: %s\n", cudaGetErrorString(cudaGetLastError())); return 1; }
+            printf("burst of 9 MMAs N=128, f16 accumulator, %2d warps reading it packed: issue %.0f clk, until complete %.0f clk per burst\n", lw, h[0] / 400.0, h[1] / 400.0);
         }
         k3<3><<<148, 256, 200 * 1024>>>(400, d, 128);
         cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
@@ -216,6 +248,12 @@ int main()
         k2<0><<<148, 256, 200 * 1024>>>(200, d, 0, 0);
         if (cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("k2<0> failed\n"); return 1; }
         printf("%-48s issue %.1f clk/MMA, complete %.1f clk/MMA\n", "one thread, unrolled, desc += 16", h[0] / 1800.0, h[1] / 1800.0);
+        for (int n : {16, 128})
+            for (int hw : {0, 16}) {
+                k2<1><<<148, 576, 200 * 1024>>>(200, d, hw, -8, n);
+                if (cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("k2<1> n failed\n"); return 1; }
+                printf("N=%3d whole warp + elect + %2d warps of HFMA2 streams: issue %.1f clk/MMA, complete %.1f clk/MMA\n", n, hw, h[0] / 1800.0, h[1] / 1800.0);
+            }
         k2<1><<<148, 256, 200 * 1024>>>(200, d, 0, 0);
         if (cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("k2<1> failed\n"); return 1; }
         printf("%-48s issue %.1f clk/MMA, complete %.1f clk/MMA\n", "whole warp + elect.sync, unrolled", h[0] / 1800.0, h[1] / 1800.0);
