@@ -114,6 +114,11 @@ class FusedDecoderBase(nn.Module):
             result[k] = {"xyz": xyz, "scale": scale, "rotation": rotation, "opacity": opacity, "color": color}[k]
         return result
 
+    def invalidate_packed_weights(self):
+        """See ``FlatParams.invalidate``: needed only after parameter writes that bypass autograd's version counters."""
+        if self._flat is not None:
+            self._flat.invalidate()
+
     def pack_planes(self, feature_planes):
         """fp32 NCHW planes -> ``fused.PackedPlanes`` (fp16 channels-last), accepted by ``decode`` / ``forward``
         (when the generator returns it as ``feature_planes``) and by ``FramePipeline.frame`` in place of the tensor."""

@@ -96,6 +96,14 @@ class FlatParams:
         self._params = [t for _, _, _, t in self._tensors(owner)]
         self._packed_version = None
 
+    def invalidate(self):
+        """Force the packed kernel weights to be rebuilt on the next decode.  The cache follows the parameters' autograd
+        version counters, which every in-place op on the parameter bumps (``optimizer.step()``, ``copy_``,
+        ``load_state_dict``); writes that bypass them — ``p.data.add_(...)``, ``flat.flat[...] = ...``, a raw CUDA copy —
+        do not, so call this after such a write (``decoder.invalidate_packed_weights()``)."""
+        self._packed_version = None
+        self._alt_packed = None
+
     def in_sync(self, owner):
         first = next(self._tensors(owner))[3]
         return self.flat is not None and first.data_ptr() == self.flat.data_ptr() and first.device == self.flat.device

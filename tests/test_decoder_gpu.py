@@ -103,6 +103,12 @@ def test_weights_update_is_seen(cuda):
             dec.color_decoder.backbone[6].bias.add_(1.0)
             b = dec.decode(planes, xyz).color
         assert torch.allclose(b - a, torch.ones_like(a), atol=atol)
+        # a write through .data does not bump the version counter the cache follows: it needs an explicit invalidate
+        with torch.no_grad():
+            dec.color_decoder.backbone[6].bias.data.sub_(1.0)
+            dec.invalidate_packed_weights()
+            c = dec.decode(planes, xyz).color
+        assert torch.allclose(c, a, atol=atol)
 
 
 def test_precision_switch_gives_consistent_results(cuda):
