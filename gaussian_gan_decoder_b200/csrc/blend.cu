@@ -22,7 +22,8 @@
 namespace ggd {
 namespace {
 
-constexpr int kBatch = kTilePixels;  // 256 instances staged per round
+constexpr int kBatch = 2 * kTilePixels;  // instances staged per round (two per thread): half as many CTA barriers as with 256,
+                                         // at which the eight warps of a tile wait for the slowest one's hit list
 
 // Conservative footprint test.  An instance can only change a pixel if
 // alpha = min(0.99, o * exp(power)) >= 1/255, i.e. d^T Q d <= 2 ln(255 o) with Q the conic.
@@ -103,18 +104,22 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
 
     for (int i = 0; i < rounds; ++i, to_do -= kBatch) {
         if (__syncthreads_count(Tg == 0.0f) == kTilePixels) break;
-        const uint32_t progress = (uint32_t)i * kBatch + tr;
-        if (range.x + progress < range.y) {
-            const uint32_t id = __ldg(point_list + range.x + progress);
-            const float2 xy = __ldg(means2D + id);
-            const float4 co = __ldg(conic_opacity + id);
-            const float r = __ldg(features + 3 * (size_t)id);
-            const float g = __ldg(features + 3 * (size_t)id + 1);
-            const float b = __ldg(features + 3 * (size_t)id + 2);
-            s_rec[3 * tr] = make_float4(xy.x, xy.y, co.x, co.y);
-            s_rec[3 * tr + 1] = make_float4(co.z, co.w, r, g);
-            s_rec[3 * tr + 2].x = b;
-            s_mask[tr] = warp_block_mask(xy.x, xy.y, co.x, co.y, co.z, co.w, tile_x0, tile_y0);
+#pragma unroll
+        for (int q = 0; q < kBatch / kTilePixels; ++q) {
+            const int slot = q * kTilePixels + tr;
+            const uint32_t progress = (uint32_t)i * kBatch + (uint32_t)slot;
+            if (range.x + progress < range.y) {
+                const uint32_t id = __ldg(point_list + range.x + progress);
+                const float2 xy = __ldg(means2D + id);
+                const float4 co = __ldg(conic_opacity + id);
+                const float r = __ldg(features + 3 * (size_t)id);
+                const float g = __ldg(features + 3 * (size_t)id + 1);
+                const float b = __ldg(features + 3 * (size_t)id + 2);
+                s_rec[3 * slot] = make_float4(xy.x, xy.y, co.x, co.y);
+                s_rec[3 * slot + 1] = make_float4(co.z, co.w, r, g);
+                s_rec[3 * slot + 2].x = b;
+                s_mask[slot] = warp_block_mask(xy.x, xy.y, co.x, co.y, co.z, co.w, tile_x0, tile_y0);
+            }
         }
         __syncthreads();
 
