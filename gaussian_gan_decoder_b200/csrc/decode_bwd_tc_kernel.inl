@@ -182,10 +182,13 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
                 epi_barrier();
                 // last-layer bias gradient, reduced over the tile (the weight gradient is an MMA issued with the next
                 // step: dW3 += H3^T dY into its own TMEM accumulator, flushed once at the end of the kernel)
-                if (colq < n_out && r == 0) {
-                    float sb = 0.f;
-                    for (int p = 0; p < kM; ++p) sb += dy32[4 * p + colq];
-                    atomicAdd(a.dflat + L.flat_b[h][3] + colq, sb);
+                // (warp w < n_out sums component w over the 128 points: 4 rows per lane, then a butterfly — one thread
+                // walking the 128 rows took ~4000 clocks per tile-head)
+                if (warp < n_out) {
+                    float sb = dy32[4 * lane + warp] + dy32[4 * (lane + 32) + warp] + dy32[4 * (lane + 64) + warp] + dy32[4 * (lane + 96) + warp];
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) sb += __shfl_xor_sync(0xffffffffu, sb, o);
+                    if (lane == 0) atomicAdd(a.dflat + L.flat_b[h][3] + warp, sb);
                 }
                 signal_ready();
                 // ---- backward: dZ_l = (dZ_{l+1} W_{l+1}) * G_l for l = 2, 1, 0 (in place over G_l) ----
