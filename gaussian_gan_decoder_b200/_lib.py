@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libggd_b200.so")
 
 GGD_OK, GGD_E_INVALID, GGD_E_CUDA, GGD_E_CAPACITY = 0, 1, 2, 3
-ABI_VERSION = 2          # ggd_abi_version() of the library these signatures describe
+ABI_VERSION = 3          # ggd_abi_version() of the library these signatures describe
 BINNING_RADIX, BINNING_AUTO, BINNING_TILES, BINNING_LEAN = 0, 1, 2, 4
 
 
@@ -74,7 +74,7 @@ SIGNATURES = {
     "ggd_mlp_forward": (_i, [_p, _p, _p, _i, _i] + [_p] * 8 + [_i, _i, _p]),
     "ggd_activation_backward": (_i, [_p, _i, _p, _p, _p, _p, _p, _p]),
     "ggd_decode_backward_scratch_bytes": (_sz, [_cfg, _i]),
-    "ggd_decode_backward": (_i, [_p, _cfg, _p, _p, _i, _p, _p] + [_p] * 10 + [_p, _sz, _p, _p]),
+    "ggd_decode_backward": (_i, [_p, _cfg, _p, _p, _p, _i, _p, _p] + [_p] * 10 + [_p, _sz, _p, _p]),
 }
 
 _lib = None

@@ -182,7 +182,7 @@ int ggd_raster_binning(int mode)
 
 const char* ggd_last_error(void) { return g_err; }
 uint64_t ggd_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
-int ggd_abi_version(void) { return 2; }
+int ggd_abi_version(void) { return 3; }
 
 int ggd_raster_workspace_sizes(int P, int W, int H, uint64_t bin_capacity, size_t sizes_out[3])
 {

@@ -108,7 +108,7 @@ size_t ggd_decode_backward_scratch_bytes(const ggd_decoder_config* cfg, int P)
     return simt > tc ? simt : tc;
 }
 
-int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl_f32,
+int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl_f32, const void* planes_cl_f16,
                         const float* xyz, int P, const float* flat_params, const float* packed_f32,
                         const float* out_xyz, const float* out_scale, const float* out_rotation,
                         const float* out_opacity, const float* out_color,
@@ -145,6 +145,7 @@ int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float
         if (int e = launch_pack_weights_tc(s, a.L, flat_params, pf)) return e;
         if (int e = launch_pack_weights_bwd_tc(s, a.L, flat_params, pb)) return e;
         t.packed_fwd = pf; t.packed_bwd = pb;
+        t.planes16 = static_cast<const __half*>(planes_cl_f16);
         if (int e = launch_decode_bwd_chain_tc(s, t, sms)) return e;
         return launch_decode_bwd_dw_mn(s, a.L, a.stage, (size_t)P, dflat, sms);
     }

@@ -88,6 +88,8 @@ struct DecodeBwdTcArgs {
     DecodeBwdArgs b;              // planes (fp32 channels-last), xyz, outs, douts, stage, dflat, dplanes
     const uint8_t* packed_fwd;    // decode_tc.cu forward pack (fp16, bias columns folded in)
     const uint8_t* packed_bwd;    // transposed fp16 pack (launch_pack_weights_bwd_tc)
+    const __half* planes16;       // optional: the forward's fp16 channels-last planes; the recompute then samples what the
+                                  // forward sampled (and half the bytes: the fp32 planes do not stay in L2 next to the staging traffic)
 };
 int launch_decode_bwd_chain_tc(cudaStream_t s, const DecodeBwdTcArgs& a, int num_sms);
 int launch_decode_bwd_dw_mn(cudaStream_t s, const DecoderLayout& L, const uint8_t* stage, size_t P, float* dflat, int num_sms);

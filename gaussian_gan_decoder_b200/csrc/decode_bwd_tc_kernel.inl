@@ -53,6 +53,15 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+#ifdef GGD_BWD_PROF
+    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long t_kernel = clock64();
+#define PROF_T(x) const long long x = clock64()
+#define PROF_ADD(k, t0) pc[k] += clock64() - (t0)
+#else
+#define PROF_T(x)
+#define PROF_ADD(k, t0)
+#endif
 
     if (warp < 16) {
         // =============================== epilogue warps ===============================
@@ -65,10 +74,12 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
         const size_t plane_stride = (size_t)a.D * a.H * a.W * kFeat;
         uint32_t n_acc = 0;
         auto wait_acc = [&]() {
+            PROF_T(tw);
             if (lane == 0) ptx::mbar_wait(&bars[B_ACC], n_acc & 1);
             __syncwarp();
             ++n_acc;
             ptx::tc_fence_after();
+            PROF_ADD(1, tw);
         };
         auto signal_ready = [&]() {
             ptx::tc_fence_before();
@@ -78,8 +89,35 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
         };
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
             const int p0 = tile * kM;
-            // ---- sampling (fp32 planes, 8 lanes per point) into the layer-0 operand ----
-            {
+            PROF_T(ts);
+            // ---- sampling into the layer-0 operand: the forward's fp16 planes when given (4 lanes per point, as in
+            // decode_tc_kernel), else the fp32 planes (8 lanes per point) ----
+            if (args.planes16) {
+                const int sub = tid & 3, pt = tid >> 2, gps = p0 + pt;
+                float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                if (gps < a.P) {
+                    const float x = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps);
+                    const float y = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps + 1);
+                    const float z = a.coord_scale * __ldg(a.xyz + 3 * (size_t)gps + 2);
+                    const __half* pl = args.planes16;
+                    if (a.arch == 0) {
+                        sample8h<1>(pl, 1, a.H, a.W, x, y, 0.f, sub, acc);
+                        sample8h<1>(pl + plane_stride, 1, a.H, a.W, x, z, 0.f, sub, acc);
+                        sample8h<1>(pl + 2 * plane_stride, 1, a.H, a.W, z, x, 0.f, sub, acc);
+                    } else {
+                        sample8h<2>(pl, a.D, a.H, a.W, x, y, z, sub, acc);
+                        sample8h<2>(pl + plane_stride, a.D, a.H, a.W, x, z, y, sub, acc);
+                        sample8h<2>(pl + 2 * plane_stride, a.D, a.H, a.W, y, z, x, sub, acc);
+                    }
+                }
+                uint32_t pk[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const __half2 hv = __floats2half2_rn(acc[2 * q] / 3.f, acc[2 * q + 1] / 3.f);
+                    pk[q] = *reinterpret_cast<const uint32_t*>(&hv);
+                }
+                *reinterpret_cast<uint4*>(X0 + canon(pt, 8 * sub, kK0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            } else {
                 const int sub = tid & 7;
                 for (int it = 0; it < 2; ++it) {
                     const int pt = it * 64 + (tid >> 3), gp = p0 + pt;
@@ -105,6 +143,8 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
                     *reinterpret_cast<uint2*>(X0 + canon(pt, 4 * sub, kK0)) =
                         make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
                 }
+            }
+            {
                 if (colq == 0) {   // position, chained inputs (saved forward results), zero padding, constant one
                     const int gp = p0 + r;
                     auto put = [&](int k, float v) { *reinterpret_cast<__half*>(X0 + canon(r, k, kK0)) = __float2half_rn(v); };
@@ -124,6 +164,7 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
                 }
             }
             signal_ready();
+            PROF_ADD(2, ts);
 
             for (int hi = kHeads - 1; hi >= 0; --hi) {
                 const int h = L.order[hi], n_out = head_out(h);
@@ -254,6 +295,11 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
         }
     }
 #include "decode_bwd_tc_roles.inl"
+#ifdef GGD_BWD_PROF
+    if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 16))
+        printf("bwd chain CTA0 warp %d: kernel %lld | wait_acc %lld sampling %lld | mma: wait_w %lld wait_ready %lld bulk_wait %lld issue %lld\n",
+               warp, clock64() - t_kernel, pc[1], pc[2], pc[3], pc[4], pc[5], pc[6]);
+#endif
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 16) ptx::tmem_dealloc<512>(tmem_base);

@@ -18,8 +18,13 @@
                     for (int s = 0; s < 8; ++s, ++cnt) {
                         const uint32_t slot = cnt % kWSlots;
                         const uint32_t w_addr = sb + kOffW + slot * kSlotBytes;
+                        PROF_T(t0);
                         ptx::mbar_wait(&bars[BW_FULL + slot], (cnt / kWSlots) & 1);
+                        PROF_ADD(3, t0);
+                        PROF_T(t1);
                         ptx::mbar_wait(&bars[B_READY], n_ready & 1);
+                        PROF_ADD(4, t1);
+                        PROF_T(t2);
                         ++n_ready;
                         ptx::tc_fence_after();
                         bool stored = false;
@@ -43,9 +48,12 @@
                             case 5: case 6: mma_k(dacc, sb + kOffDZ, kHidden, w_addr, kHidden, id128, integral_constant<int, kHidden / 16>{}, false); break;
                             default: mma_k(tmem_base + kColDX, sb + kOffDZ, kHidden, w_addr, kHidden, id48, integral_constant<int, kHidden / 16>{}, hi != kHeads - 1); break;
                         }
-                        if (stored) bulk_wait_read();
+                        PROF_T(t3);
+                        if (stored) bulk_wait_read();      // measured: committing first and letting the epilogue wait for the
+                        PROF_ADD(5, t3);                   // drain right before it overwrites the source changes nothing
                         ptx::mma_commit(&bars[B_ACC]);
                         ptx::mma_commit(&bars[BW_EMPTY + slot]);
+                        PROF_ADD(6, t2);
                     }
                 }
             }

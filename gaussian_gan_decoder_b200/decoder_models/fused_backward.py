@@ -66,9 +66,13 @@ def decode_backward(owner, planes, xyz, outs, douts, want_dplanes):
         _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg32), p(planes), p(planes_cl)))
         packed32 = flat.packed_weights_for(cfg32)
         cfg = owner._cfg_for(planes)            # its precision picks the backward flavour
+        planes_cl16 = None
+        if cfg.precision == 1:                  # the tensor-core chain recomputes from the planes the fp16 forward sampled
+            planes_cl16 = torch.empty(planes.numel() * 2, dtype=torch.uint8, device=dev)
+            _lib.check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes), p(planes_cl16)))
         nbytes = lib.ggd_decode_backward_scratch_bytes(C.byref(cfg), P)
         scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        _lib.check(lib.ggd_decode_backward(s, C.byref(cfg), p(planes_cl), p(xyz), P, p(flat.flat), p(packed32),
+        _lib.check(lib.ggd_decode_backward(s, C.byref(cfg), p(planes_cl), p(planes_cl16), p(xyz), P, p(flat.flat), p(packed32),
                                            p(outs[0]), p(outs[1]), p(outs[2]), p(outs[3]), p(outs[4]),
                                            p(douts[0]), p(douts[1]), p(douts[2]), p(douts[3]), p(douts[4]),
                                            p(scratch), nbytes, p(dflat), p(dplanes)))

@@ -147,7 +147,7 @@ class TrainPipeline:
         check(lib.ggd_activation_backward(s, P, p(a["scale"]), p(o["rotation"]), p(a["opacity"]),
                                           p(g["scale"]), p(g["rot"]), p(g["opacity"])))
         # decoder backward straight into the flat gradient buffer the parameters' .grad tensors view
-        check(lib.ggd_decode_backward(s, C.byref(cfg), p(self.planes32), p(xyz), P, p(flat.flat), p(flat.packed_weights_for(cfg32)),
+        check(lib.ggd_decode_backward(s, C.byref(cfg), p(self.planes32), p(self.planes16) if cfg.precision == 1 else None, p(xyz), P, p(flat.flat), p(flat.packed_weights_for(cfg32)),
                                       p(o["xyz"]), p(o["scale"]), p(o["rotation"]), p(o["opacity"]), p(o["color"]),
                                       p(g["mean3D"]), p(g["scale"]), p(g["rot"]), p(g["opacity"]), p(g["sh"]),
                                       p(self.scratch), self.scratch.numel(), p(flat.flat_grad), None))

@@ -320,6 +320,9 @@ GGD_API int ggd_mlp_forward(void* stream, const float* tri_features, const float
  * the sequential variants) and grid_sample backward.  No gradient flows to
  * init_position, as in the reference (it is an input).
  *   planes_cl_f32 : fp32 channels-last planes (ggd_planes_channels_last, precision 0)
+ *   planes_cl_f16 : optional (may be NULL): the fp16 channels-last planes the fp16 forward sampled (precision 1).  The
+ *                   tensor-core chain then recomputes the forward from exactly what the forward read, at half the bytes
+ *                   (measured: its plane sampling drops from 29 % of the kernel to 5 %); ignored by the fp32 chain
  *   packed_f32    : ggd_decode_pack_weights output for precision 0
  *   out_*         : the forward results (the chained variants feed them to later heads)
  *   dL_d*         : gradients of the five results; any may be NULL (= zero)
@@ -331,7 +334,7 @@ GGD_API int ggd_mlp_forward(void* stream, const float* tri_features, const float
  * fp32 channels-last ones and the weight gradients are accumulated on tensor cores. */
 GGD_API size_t ggd_decode_backward_scratch_bytes(const ggd_decoder_config* cfg, int P);
 GGD_API int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float* planes_cl_f32,
-                                const float* xyz, int P, const float* flat_params, const float* packed_f32,
+                                const void* planes_cl_f16, const float* xyz, int P, const float* flat_params, const float* packed_f32,
                                 const float* out_xyz, const float* out_scale, const float* out_rotation,
                                 const float* out_opacity, const float* out_color,
                                 const float* dL_dxyz, const float* dL_dscale, const float* dL_drotation,
