@@ -145,22 +145,37 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
                 }
             }
             {
-                if (colq == 0) {   // position, chained inputs (saved forward results), zero padding, constant one
+                if (colq == 0) {   // columns 32..47: position, chained inputs (saved forward results), zero padding, constant one
                     const int gp = p0 + r;
-                    auto put = [&](int k, float v) { *reinterpret_cast<__half*>(X0 + canon(r, k, kK0)) = __float2half_rn(v); };
-                    for (int k = kFeat; k < kK0 - 1; ++k) put(k, 0.f);
+                    float f[16];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) f[k] = 0.f;
+                    f[15] = 1.0f;
                     if (gp < a.P) {
-                        for (int j = 0; j < 3; ++j) put(kFeat + j, __ldg(a.xyz + 3 * (size_t)gp + j));
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) f[j] = __ldg(a.xyz + 3 * (size_t)gp + j);
                         if (L.variant != 0) {
-                            int col = chain0;
+                            int col = 3;      // chain0 - kFeat
+#pragma unroll
                             for (int hi = 0; hi < kHeads - 1; ++hi) {
                                 const int h = L.order[hi], n = head_out(h);
-                                for (int j = 0; j < n; ++j) put(col + j, __ldg(a.out[h] + (size_t)gp * n + j));
+                                for (int j = 0; j < n; ++j) {
+                                    const float v = __ldg(a.out[h] + (size_t)gp * n + j);
+#pragma unroll
+                                    for (int k = 3; k < 15; ++k) if (k == col + j) f[k] = v;     // static register indexing
+                                }
                                 col += n;
                             }
                         }
                     }
-                    put(kK0 - 1, 1.0f);
+                    uint32_t w[8];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const __half2 hv = __floats2half2_rn(f[2 * q], f[2 * q + 1]);
+                        w[q] = *reinterpret_cast<const uint32_t*>(&hv);
+                    }
+                    *reinterpret_cast<uint4*>(X0 + canon(r, kFeat, kK0)) = make_uint4(w[0], w[1], w[2], w[3]);
+                    *reinterpret_cast<uint4*>(X0 + canon(r, kFeat + 8, kK0)) = make_uint4(w[4], w[5], w[6], w[7]);
                 }
             }
             signal_ready();
