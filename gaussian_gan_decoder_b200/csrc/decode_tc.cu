@@ -7,18 +7,23 @@
 // Structure (one persistent CTA per SM, 18 warps):
 //   warps 0-15       epilogue: thread = one point (TMEM lane) x one quarter of the 128 accumulator
 //                    columns.  They sample the planes into the layer-0 operands, turn an
-//                    accumulator into the next layer's fp16 operand (GELU in half2 with MUFU
-//                    tanh) and apply the head post-math.  Two 128-point tiles ("slots", each with
-//                    its own operand buffer and TMEM accumulator) are in flight: while all 16
-//                    warps convert slot A, the tensor core runs slot B's MMAs, and vice versa.
-//   warp 16          one thread issues tcgen05.mma (M=128, N=128 or 16, K=16 per instruction)
+//                    accumulator into the next layer's fp16 operand (GELU in half2 on the FMA pipe:
+//                    gelu_poly_h2) and apply the head post-math (one output component per warp of a
+//                    lane quarter).  Three 128-point tiles ("slots", each with its own operand stage
+//                    and TMEM accumulator) are in flight, layer by layer: while the warps convert one
+//                    slot, the tensor core runs the other slots' MMAs.
+//   warp 16          one thread issues tcgen05.mma (M=128, N=128 or 16, K=16 per instruction) from
+//                    descriptors built once per tile-layer, K loop unrolled (ptx::mma_f16_ss_steps)
 //   warp 17          one thread streams the packed fp16 weights of the current head, layer by
 //                    layer, with 1-D bulk async copies into four shared-memory slots; a slot
 //                    is refilled with the next head's layer as soon as its last MMA retired.
-// A group of T tiles (T*128 points) shares every weight load, which is what keeps the
-// L2 -> shared traffic (445 KB per head set) off the critical path.
+// A group of three tiles (384 points), one per slot, shares every weight load.
 // Operands use the K-major, no-swizzle canonical layout (8x16-byte core matrices); biases are
-// folded into the GEMMs through a constant-one operand column.
+// folded into the GEMMs: the weights carry a bias column block, whose A-side partner is a
+// constant-one column of the layer-0 operand and, for the hidden layers, one 4 KB constant-one
+// block shared by all slots (a ninth K step).
+// Shared memory (T = 3, no positional embedding): 256 B barriers + 90,624 B weights + 3 x 32,768 B
+// operand stages + 4,096 B ones block + 3 x 12,288 B layer-0 operands = 230,144 B of 232,448.
 #include "decode_args.cuh"
 #include "sampling.cuh"
 #include "tc_ptx.cuh"
