@@ -138,6 +138,7 @@ struct PreprocessArgs {
     int grid_x, grid_y;
     uint32_t* tile_counts;   // optional [grid_x * grid_y][32]: word 0 += 1 for every tile a splat touches
     uint32_t* counts_valid;  // set to 1 by the kernel when tile_counts were written (GeomState::counters[12])
+    int hist_tiles;          // set by launch_preprocess: size of the CTA-local tile histogram (0 = none)
 };
 int launch_preprocess(cudaStream_t s, const PreprocessArgs& a, const GeomState& g, int* radii);
 int launch_scan(cudaStream_t s, int P, const GeomState& g);

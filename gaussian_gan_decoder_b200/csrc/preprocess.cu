@@ -153,6 +153,7 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
     __shared__ __align__(16) float s_cov[kThreads * 6];   // in: scales (3/pt) or cov3D_precomp (6/pt); out: cov3D
     __shared__ __align__(16) float s_col[kThreads * 3];   // in: SH dc (M==1) ; out: rgb
     __shared__ __align__(16) uint8_t s_clamp[kThreads * 3];
+    extern __shared__ uint32_t s_cnt[];   // [a.hist_tiles] CTA-local tile histogram (dense frames, see below)
 
     const int base = blockIdx.x * kThreads;
     const int n_here = min(kThreads, a.P - base);
@@ -171,6 +172,7 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
 
     int my_radius_i = 0;
     uint32_t my_tiles = 0;
+    uint2 my_rmin = make_uint2(0u, 0u), my_rmax = make_uint2(0u, 0u);
     float cov6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float col3[3] = {0.f, 0.f, 0.f};
     bool col_valid = false, cov_valid = false;
@@ -272,14 +274,35 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
                     conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, __ldg(a.opacities + idx));
                     my_radius_i = (int)my_radius;
                     my_tiles = area;
-                    if (a.tile_counts)   // per-tile list lengths for tile_binning.cu
-                        for (uint32_t ty = rmin.y; ty < rmax.y; ++ty)
-                            for (uint32_t tx = rmin.x; tx < rmax.x; ++tx) atomicAdd(a.tile_counts + (size_t)(ty * a.grid_x + tx) * 32, 1u);
+                    my_rmin = rmin; my_rmax = rmax;
                 }
             }
         }
         radii[idx] = my_radius_i;
         tiles_touched[idx] = my_tiles;
+    }
+
+    // per-tile list lengths for tile_binning.cu.  A frame of small splats (the random-init decoder: 1.6 tiles per
+    // Gaussian) adds one global atomic per (splat, tile).  A frame of large splats (trained-like: 13 tiles per Gaussian,
+    // 6.4 M instances on 1024 counters) would serialise on those counters: there the CTA counts into a shared-memory
+    // histogram first and flushes one atomic per non-empty tile (~3x fewer, each carrying a count).  The choice is per
+    // CTA, from its own splats.
+    if (a.tile_counts) {
+        const bool dense = a.hist_tiles > 0 && __syncthreads_count(my_tiles > 4u) >= kThreads / 2;
+        if (dense) {
+            for (int i = t; i < a.hist_tiles; i += kThreads) s_cnt[i] = 0u;
+            __syncthreads();
+            for (uint32_t ty = my_rmin.y; ty < my_rmax.y; ++ty)
+                for (uint32_t tx = my_rmin.x; tx < my_rmax.x; ++tx) atomicAdd(&s_cnt[ty * a.grid_x + tx], 1u);
+            __syncthreads();
+            for (int i = t; i < a.hist_tiles; i += kThreads) {
+                const uint32_t c = s_cnt[i];
+                if (c) atomicAdd(a.tile_counts + (size_t)i * 32, c);
+            }
+        } else {
+            for (uint32_t ty = my_rmin.y; ty < my_rmax.y; ++ty)
+                for (uint32_t tx = my_rmin.x; tx < my_rmax.x; ++tx) atomicAdd(a.tile_counts + (size_t)(ty * a.grid_x + tx) * 32, 1u);
+        }
     }
 
     // staged, coalesced write-back of the stride-3/6 outputs. Lanes that did not
@@ -423,7 +446,10 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ pts, const 
 int launch_preprocess(cudaStream_t s, const PreprocessArgs& a, const GeomState& g, int* radii)
 {
     const int blocks = (a.P + kThreads - 1) / kThreads;
-    preprocess_kernel<<<blocks, kThreads, 0, s>>>(a, g.depths, radii, g.means2D, g.cov3D,
+    PreprocessArgs b = a;
+    const int tiles = a.grid_x * a.grid_y;
+    b.hist_tiles = (a.tile_counts && tiles <= 4096) ? tiles : 0;      // 16 KB of dynamic shared memory at most
+    preprocess_kernel<<<blocks, kThreads, sizeof(uint32_t) * (size_t)b.hist_tiles, s>>>(b, g.depths, radii, g.means2D, g.cov3D,
                                                   g.conic_opacity, g.rgb, g.tiles_touched, g.clamped);
     GGD_LAUNCH_CHECK("preprocess_kernel");
     return GGD_OK;
