@@ -17,10 +17,6 @@ ARCHS = {"eg3d": 0, "panohead": 1}
 DecoderConfig = _lib.DecoderConfig
 
 
-def _bind(lib):
-    """signatures are bound by _lib.load()"""
-
-
 PRECISIONS = {"fp32": 0, "fp16": 1}
 # "fp16": tcgen05 tensor-core kernel (fp16 operands, fp32 accumulation) — the production path.
 # "fp32": exact CUDA-core kernel — the accuracy anchor.  Overridable per decoder (``.precision``).
@@ -33,14 +29,14 @@ def make_config(arch, variant, depth, h, w, pos_freqs, hidden, box_warp, scale_b
 
 
 def param_counts(cfg):
-    lib = _lib.load(); _bind(lib)
+    lib = _lib.load()
     a, b = C.c_size_t(), C.c_size_t()
     _lib.check(lib.ggd_decode_param_counts(C.byref(cfg), C.byref(a), C.byref(b)))
     return a.value, b.value
 
 
 def param_offset(cfg, head, layer, is_bias):
-    lib = _lib.load(); _bind(lib)
+    lib = _lib.load()
     off, fi, fo = C.c_size_t(), C.c_int(), C.c_int()
     _lib.check(lib.ggd_decode_param_offset(C.byref(cfg), head, layer, int(is_bias), C.byref(off), C.byref(fi), C.byref(fo)))
     return off.value, fi.value, fo.value
@@ -128,7 +124,7 @@ class FlatParams:
         # parameters are views of the flat buffer but carry their own version counters
         ver = sum(t._version for t in self._params)
         if self.packed is None or self.packed.device != self.flat.device or self._packed_version != ver:
-            lib = _lib.load(); _bind(lib)
+            lib = _lib.load()
             if self.packed is None or self.packed.device != self.flat.device:
                 self.packed = torch.empty(self.packed_count, dtype=torch.float32, device=self.flat.device)
             with torch.cuda.device(self.flat.device):
@@ -162,7 +158,7 @@ class PackedPlanes:
 
 def pack_planes(cfg, planes_nchw):
     """fp32 NCHW planes (device) -> PackedPlanes; cfg must be an fp16-precision config."""
-    lib = _lib.load(); _bind(lib)
+    lib = _lib.load()
     if cfg.precision != 1:
         raise ValueError("packed planes are the fp16 tensor-core path's layout")
     planes_nchw = planes_nchw.to(torch.float32).contiguous()
@@ -175,7 +171,7 @@ def pack_planes(cfg, planes_nchw):
 def decode_forward(cfg, planes_nchw, xyz, packed, with_activations=True):
     """planes [1,3,32*D,H,W] fp32 (generator layout) or PackedPlanes, xyz [P,3] -> dict of raw attributes
     (+ activated scale/rotation/opacity for the rasteriser)."""
-    lib = _lib.load(); _bind(lib)
+    lib = _lib.load()
     if not xyz.is_cuda:
         raise RuntimeError("init_position must be a CUDA tensor: the decoder has no CPU path")
     dev = xyz.device
