@@ -151,7 +151,8 @@ int launch_tile_ranges(cudaStream_t s, const GeomState& g, const BinState& b, ui
 // per-tile binning (tile_binning.cu)
 constexpr uint32_t kTileCountStride = 32;  // words between two tiles' counters
 constexpr uint32_t kTileSortMax = 4096;   // longest tile list the register-resident shared-memory sort takes
-constexpr uint32_t kTileSortLargeMax = 24576;   // longest list of the one-CTA-per-SM variant (192 KB of words + 32 KB of buckets)
+constexpr uint32_t kTileSortLargeMax = 24576;   // words the one-CTA-per-SM variant sorts at once (192 KB of words + 32 KB of buckets)
+constexpr uint32_t kTileSortHugeMax = 4 * kTileSortLargeMax;   // longest list of the per-tile path: sorted in depth chunks of <= kTileSortLargeMax
 int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int tiles, uint64_t capacity, int P, bool strict);
 int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g, const int* radii,
                         const BinState& b, const ImgState& im, uint64_t capacity, bool ref_order_arrays);

@@ -15,15 +15,16 @@
 //   preprocess        counts instances per tile (atomics, fused into the projection kernel)
 //   tile_scan_kernel  exclusive scan of the counts -> ranges[tile] = [start, end) ((0,0) for an empty
 //                     tile, as the reference leaves it); sets up each tile's write cursor; decides
-//                     whether the frame qualifies (longest list <= kTileSortLargeMax,
+//                     whether the frame qualifies (longest list <= kTileSortHugeMax,
 //                     R <= capacity)
 //   tile_scatter      slot-centric like duplicate_kernel; claims a slot in the tile's segment with an
 //                     atomic on the tile's cursor
 //   tile_sort_kernel  one CTA per tile: distribution sort of the 64-bit words in shared memory (bitonic
 //                     network for lists with heavily clustered depths)
-//   tile_sort_large_kernel  the same for lists of 4097..24576 instances: persistent CTAs of 1024 threads,
-//                     one per SM, walk the list of long tiles the scan wrote
-// Frames that do not qualify (a tile list longer than kTileSortLargeMax) take the radix path of binning.cu;
+//   tile_sort_large_kernel  the same for lists of 4097..98304 instances: persistent CTAs of 1024 threads,
+//                     one per SM, walk the list of long tiles the scan wrote; lists beyond 24576 words are
+//                     sorted in depth chunks
+// Frames that do not qualify (a tile list longer than kTileSortHugeMax) take the radix path of binning.cu;
 // the decision is made on the device (counters[4]) and both sets of kernels are always enqueued, the
 // ones that do not apply return at once, so no host round trip is needed.
 #include "common.cuh"
@@ -52,7 +53,7 @@ tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int 
         const uint32_t R = P > 0 ? __ldg(offsets + P - 1) : 0u;
         // counters[12]: preprocess counted the tile lists of THIS frame (it does so only when asked to); without it
         // the counts are the zeros of the frame's memset and must not be taken for an empty frame
-        const bool per_tile = counters[12] != 0u && m <= kTileSortLargeMax && R <= capacity;
+        const bool per_tile = counters[12] != 0u && m <= kTileSortHugeMax && R <= capacity;
         s_max = per_tile ? 1u : 0u;
         s_carry = 0;
         s_large = 0;
@@ -437,7 +438,8 @@ __device__ void cta_sort_range(uint64_t* __restrict__ s, uint32_t m)
 
 __global__ void __launch_bounds__(kLargeThreads, 1)
 tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ words, uint64_t* __restrict__ keys,
-                       uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters, const uint32_t* __restrict__ tile_list)
+                       uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters, const uint32_t* __restrict__ tile_list,
+                       uint32_t* __restrict__ status_flags)
 {
     if (__ldg(counters + 4) == 0u) return;
     extern __shared__ __align__(16) uint8_t s_dyn[];
@@ -478,74 +480,124 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
             dmax = max(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
         }
         if (lane == 0) { s_red[0][warp] = dmin; s_red[1][warp] = dmax; }
-        for (uint32_t i = t; i < kLargeBuckets; i += kLargeThreads) s_hist[i] = 0;
-        if (t == 0) s_nbig = 0;
         if (t < kCoarse) s_c[t] = 0;
         __syncthreads();
         for (int k = 0; k < kLargeThreads / 32; ++k) { dmin = min(dmin, s_red[0][k]); dmax = max(dmax, s_red[1][k]); }
-        BucketMap map{dmin, (float)kCoarse / ((float)(dmax - dmin) + 1.0f), (float)kLargeBuckets / (float)n, s_cstart, kLargeBuckets};
-        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_c[map.coarse((uint32_t)(src[i] >> 32))], 1u);
+        const float scale_c = (float)kCoarse / ((float)(dmax - dmin) + 1.0f);
+        auto coarse_of = [&](uint64_t w) { return min((uint32_t)(kCoarse - 1), (uint32_t)((float)((uint32_t)(w >> 32) - dmin) * scale_c)); };
+        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_c[coarse_of(src[i])], 1u);
         __syncthreads();
         coarse_scan(s_c, s_cstart);
         __syncthreads();
-        auto bucket = [&](uint64_t w) { return map((uint32_t)(w >> 32)); };
-        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_hist[bucket(src[i])], 1u);
-        __syncthreads();
-        // exclusive scan; thread t owns buckets [t kPer, (t + 1) kPer)
-        uint32_t cnt[kPer], sum = 0;
-#pragma unroll
-        for (int q = 0; q < kPer; ++q) { cnt[q] = s_hist[t * kPer + q]; sum += cnt[q]; }
-        uint32_t incl = sum;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
-        }
-        if (lane == 31) s_part[warp] = incl;
-        __syncthreads();
-        uint32_t start = incl - sum;
-        for (int k = 0; k < warp; ++k) start += s_part[k];
-        {
-            uint32_t run = start;
-#pragma unroll
-            for (int q = 0; q < kPer; ++q) { s_hist[t * kPer + q] = run; run += cnt[q]; }
-        }
-        __syncthreads();
-        for (uint32_t i = t; i < n; i += kLargeThreads) {
-            const uint64_t w = src[i];
-            s_out[atomicAdd(&s_hist[bucket(w)], 1u)] = w;
-        }
-        __syncthreads();
-        {
-            uint32_t b0 = start;
-#pragma unroll
-            for (int q = 0; q < kPer; ++q) {
-                const uint32_t m = cnt[q];
-                if (m > kLargeInsertMax) {
-                    const uint32_t slot = atomicAdd(&s_nbig, 1u);
-                    if (slot < 32) { s_big[2 * slot] = b0; s_big[2 * slot + 1] = m; }
-                } else {
-                    for (uint32_t i = 1; i < m; ++i) {
-                        const uint64_t x = s_out[b0 + i];
-                        uint32_t j = i;
-                        while (j > 0 && s_out[b0 + j - 1] > x) { s_out[b0 + j] = s_out[b0 + j - 1]; --j; }
-                        s_out[b0 + j] = x;
+        // A list longer than the shared-memory buffer is sorted in depth chunks: runs of coarse bins [c0, c1) holding at
+        // most kTileSortLargeMax words each, one after the other (a coarse bin is monotone in depth and equal depths share
+        // a bin, so the chunks' sorted runs concatenate to the sorted list).  Every chunk re-reads the list from L2.
+        uint32_t c0 = 0;
+        while (c0 < (uint32_t)kCoarse) {
+            uint32_t c1 = kCoarse;                      // a list that fits the buffer is one chunk: no walk over the bins
+            if (n > kTileSortLargeMax) {
+                c1 = c0 + 1;
+                while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] - s_cstart[c0] <= kTileSortLargeMax) ++c1;
+            }
+            const uint32_t first = s_cstart[c0], m_chunk = s_cstart[c1] - first;
+            const bool whole = (c0 == 0 && c1 == (uint32_t)kCoarse);
+            if (m_chunk == 0) { c0 = c1; continue; }
+            if (m_chunk > kTileSortLargeMax) {
+                // one coarse bin (1/128 of the list's depth interval) alone overflows the buffer: depths this clustered are
+                // not sorted here.  Status flag 8 tells the caller to render the frame with the radix path (mode 0).
+                // The chunk is still copied out (unsorted) so that the kernels queued behind this one read valid indices.
+                if (t == 0) { atomicOr(status_flags, 8u); s_nbig = 0; }
+                __syncthreads();
+                for (uint32_t i = t; i < n; i += kLargeThreads) {
+                    const uint64_t w = src[i];
+                    const uint32_t kc = coarse_of(w);
+                    if (kc >= c0 && kc < c1) {
+                        const uint32_t pos = atomicAdd(&s_nbig, 1u);
+                        vals[range.x + first + pos] = (uint32_t)w;
+                        keys[range.x + first + pos] = ((uint64_t)tile << 32) | (w >> 32);
                     }
                 }
-                b0 += m;
+                __syncthreads();
+                c0 = c1;
+                continue;
             }
-        }
-        __syncthreads();
-        const uint32_t nbig = s_nbig;
-        if (nbig > 32) {
-            cta_sort_range(s_out, n);                     // hopelessly clustered: sort the whole list
-        } else {
-            for (uint32_t k = 0; k < nbig; ++k) cta_sort_range(s_out + s_big[2 * k], s_big[2 * k + 1]);
-        }
-        for (uint32_t i = t; i < n; i += kLargeThreads) {
-            const uint64_t x = s_out[i];
-            vals[range.x + i] = (uint32_t)x;
-            keys[range.x + i] = ((uint64_t)tile << 32) | (x >> 32);
+            for (uint32_t i = t; i < kLargeBuckets; i += kLargeThreads) s_hist[i] = 0;
+            if (t == 0) s_nbig = 0;
+            __syncthreads();
+            // buckets even out the chunk's load through the same piecewise-linear CDF estimate as BucketMap
+            const float ratio = (float)kLargeBuckets / (float)m_chunk;
+            auto bucket = [&](uint64_t w, uint32_t& kc) {      // one evaluation of the depth's position serves bin and bucket
+                const float x = (float)((uint32_t)(w >> 32) - dmin) * scale_c;
+                kc = min((uint32_t)(kCoarse - 1), (uint32_t)x);
+                const float below = (float)(s_cstart[kc] - first), in_bin = (float)(s_cstart[kc + 1] - s_cstart[kc]);
+                return min(kLargeBuckets - 1u, (uint32_t)((below + (x - (float)kc) * in_bin) * ratio));
+            };
+            for (uint32_t i = t; i < n; i += kLargeThreads) {
+                uint32_t kc;
+                const uint32_t bk = bucket(src[i], kc);
+                if (whole || (kc >= c0 && kc < c1)) atomicAdd(&s_hist[bk], 1u);
+            }
+            __syncthreads();
+            // exclusive scan; thread t owns buckets [t kPer, (t + 1) kPer)
+            uint32_t cnt[kPer], sum = 0;
+#pragma unroll
+            for (int q = 0; q < kPer; ++q) { cnt[q] = s_hist[t * kPer + q]; sum += cnt[q]; }
+            uint32_t incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            if (lane == 31) s_part[warp] = incl;
+            __syncthreads();
+            uint32_t start = incl - sum;
+            for (int k = 0; k < warp; ++k) start += s_part[k];
+            {
+                uint32_t run = start;
+#pragma unroll
+                for (int q = 0; q < kPer; ++q) { s_hist[t * kPer + q] = run; run += cnt[q]; }
+            }
+            __syncthreads();
+            for (uint32_t i = t; i < n; i += kLargeThreads) {
+                const uint64_t w = src[i];
+                uint32_t kc;
+                const uint32_t bk = bucket(w, kc);
+                if (whole || (kc >= c0 && kc < c1)) s_out[atomicAdd(&s_hist[bk], 1u)] = w;
+            }
+            __syncthreads();
+            {
+                uint32_t b0 = start;
+#pragma unroll
+                for (int q = 0; q < kPer; ++q) {
+                    const uint32_t m = cnt[q];
+                    if (m > kLargeInsertMax) {
+                        const uint32_t slot = atomicAdd(&s_nbig, 1u);
+                        if (slot < 32) { s_big[2 * slot] = b0; s_big[2 * slot + 1] = m; }
+                    } else {
+                        for (uint32_t i = 1; i < m; ++i) {
+                            const uint64_t x = s_out[b0 + i];
+                            uint32_t j = i;
+                            while (j > 0 && s_out[b0 + j - 1] > x) { s_out[b0 + j] = s_out[b0 + j - 1]; --j; }
+                            s_out[b0 + j] = x;
+                        }
+                    }
+                    b0 += m;
+                }
+            }
+            __syncthreads();
+            const uint32_t nbig = s_nbig;
+            if (nbig > 32) {
+                cta_sort_range(s_out, m_chunk);               // hopelessly clustered: sort the whole chunk
+            } else {
+                for (uint32_t k = 0; k < nbig; ++k) cta_sort_range(s_out + s_big[2 * k], s_big[2 * k + 1]);
+            }
+            for (uint32_t i = t; i < m_chunk; i += kLargeThreads) {
+                const uint64_t x = s_out[i];
+                vals[range.x + first + i] = (uint32_t)x;
+                keys[range.x + first + i] = ((uint64_t)tile << 32) | (x >> 32);
+            }
+            __syncthreads();
+            c0 = c1;
         }
         __syncthreads();
     }
@@ -583,8 +635,9 @@ int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, cons
     GGD_CUDA_CHECK(cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_large));
     int sms = 148;
     { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    // (the flag word is counters[1]; passed as its own pointer because `counters` is read through the read-only path)
     tile_sort_large_kernel<<<std::min(tiles, sms), kLargeThreads, smem_large, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters,
-                                                                                  g.tile_counts);
+                                                                                  g.tile_counts, g.counters + 1);
     GGD_LAUNCH_CHECK("tile_sort_large_kernel");
     return GGD_OK;
 }

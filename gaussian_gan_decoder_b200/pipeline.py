@@ -119,7 +119,9 @@ class FramePipeline:
             s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
             _lib.check(self.lib.ggd_raster_status(s, _lib.ptr(self.geom), self.P, st))
             _lib.check(self.lib.ggd_raster_binning_info(s, _lib.ptr(self.geom), self.P, info))
-            if st[1] & 2:
+            if st[1] & 8:        # depths too clustered for the chunked long-list sort: this scene needs the radix sort
+                self.bin_mode, over = 0, True
+            elif st[1] & 2:
                 self.bin_mode, over = 1, True
             elif self.bin_mode == 1 and info[0] and not over:
                 self.bin_mode = 2

@@ -164,9 +164,14 @@ class _CNamespace:
                 torch.cuda.current_stream().synchronize()
             _capacity_hint[key] = max(int(R * 1.25) + 4096, 4096)
             if mode:
-                info = (C.c_uint32 * 2)()
+                info, st = (C.c_uint32 * 2)(), (C.c_uint32 * 2)()
                 _lib.check(lib.ggd_raster_binning_info(s, p(geom), P, info))
+                _lib.check(lib.ggd_raster_status(s, p(geom), P, st))
                 bh[0] = 1 if info[0] else 0
+                if st[1] & 8:      # per-tile sort refused a list (depths too clustered): render again with the radix sort
+                    mode, bh[0] = 0, 0
+                    binning = render(cap)
+                    torch.cuda.current_stream().synchronize()
         # capacity travels with the buffer so backward can re-carve it
         binning.ggd_capacity = cap
         return R, out_color, radii, geom, binning, img

@@ -133,13 +133,14 @@ GGD_API int ggd_raster_backward(void* stream, int P, int D, int M, const float* 
 
 /* Blocking read-back of { num_rendered, flags } from geom_ws (synchronises `stream`).  flags: 1 = more
  * instances than bin_capacity, 2 = mode 2 frame that needs the radix kernels, 4 = the per-tile counts in
- * geom_ws do not add up to num_rendered (state buffers of different frames were mixed); with any flag
- * set the image is undefined.  The reference returns num_rendered from forward
+ * geom_ws do not add up to num_rendered (state buffers of different frames were mixed), 8 = a tile list longer
+ * than 24576 has more than 24576 instances inside 1/128 of its depth interval (the per-tile sort does not take
+ * that: render the frame again with GGD_BINNING_RADIX); with any flag set the image is undefined.  The reference returns num_rendered from forward
  * (rasterizer_impl.cu:336); here it is a separate, optional query. */
 GGD_API int ggd_raster_status(void* stream, const void* geom_ws, int P, uint32_t out[2]);
 
 /* How stage 2 orders the instances — the `binning` argument of the three entry points above.
- * GGD_BINNING_AUTO (1): frames whose longest tile list is at most 24576 are binned per tile and each
+ * GGD_BINNING_AUTO (1): frames whose longest tile list is at most 98304 are binned per tile and each
  * list is sorted in shared memory (csrc/tile_binning.cu); other frames take the global radix sort;
  * the per-frame choice is made on the device.  GGD_BINNING_RADIX (0): always the radix sort.  Both
  * produce the bits of the reference's duplicateWithKeys + stable SortPairs + identifyTileRanges

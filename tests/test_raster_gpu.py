@@ -92,9 +92,9 @@ def test_bit_exact_full_size_config2(cuda):
 @pytest.mark.parametrize("mode", [0, 1])
 def test_bit_exact_config5_2048_2M(cuda, mode):
     """BASELINE configs[4]: 2M trained-like Gaussians at 2048x2048 (16384 tiles -> 47-bit keys, ~2.8e8 instances,
-    tile lists beyond the per-tile path's 24576 limit, the large-capacity digit pass) — every integer and float
-    stage bit for bit against the reference CUDA build, with the radix sort pinned (mode 0) and with the
-    device-side choice (mode 1).  Follows rasterizer_impl.cu:300-308 (getHigherMsb, sort bit range) and
+    tile lists beyond the 24576 words the long-list sort holds at once, the large-capacity digit pass) — every integer
+    and float stage bit for bit against the reference CUDA build, with the radix sort pinned (mode 0) and with the
+    device-side choice (mode 1: per-tile binning, the longest lists sorted in depth chunks).  Follows rasterizer_impl.cu:300-308 (getHigherMsb, sort bit range) and
     forward.cu:261-374."""
     lib = _lib.load()
     P = 2_000_000
@@ -113,8 +113,8 @@ def test_bit_exact_config5_2048_2M(cuda, mode):
     assert_bit_exact(ours, ref, P)
     rng = ours["ranges"].view(-1, 2).long()
     assert rng.shape[0] == 128 * 128 and int((rng[:, 1] - rng[:, 0]).max()) > 24576
-    if mode == 1:
-        assert info[0] == 0 and info[1] > 24576      # counted per tile, found too long, radix path taken on the device
+    if mode == 1:    # lists beyond the 24576-word shared-memory buffer are sorted per tile in depth chunks
+        assert info[0] == 1 and 24576 < info[1] <= 98304
     del ours, ref
     torch.cuda.empty_cache()
 
@@ -324,7 +324,8 @@ def test_mark_visible_bit_exact_vs_reference_cuda(cuda):
 @pytest.mark.parametrize("P,size,trained,expect_per_tile", [
     (257, 100, True, True), (50000, 512, False, True), (500_000, 512, False, True),
     (500_000, 512, True, True),      # trained-like splats: tile lists of 5-10k instances (long-list kernel)
-    (400_000, 64, True, False),      # 16 tiles only: lists far longer than the shared-memory sorts take
+    (400_000, 64, True, True),       # 16 tiles only: lists of ~50k, sorted per tile in depth chunks of <= 24576
+    (1_200_000, 32, True, False),    # 4 tiles: lists far longer than the per-tile path takes at all (> 98304)
 ])
 def test_binning_modes_agree(cuda, P, size, trained, expect_per_tile):
     """Per-tile binning (tile_binning.cu) and the global radix sort give the same bits; the per-frame choice
@@ -340,7 +341,7 @@ def test_binning_modes_agree(cuda, P, size, trained, expect_per_tile):
         info = (C.c_uint32 * 2)()
         _lib.check(lib.ggd_raster_binning_info(None, C.c_void_p(auto["_buffers"][0].data_ptr()), P, info))
         assert bool(info[0]) == expect_per_tile, (info[0], info[1])
-        assert (info[1] <= 24576) == expect_per_tile
+        assert (info[1] <= 98304) == expect_per_tile      # kTileSortHugeMax
         lib.ggd_raster_binning(0)
         radix = run_ours(s, cuda)
     finally:
@@ -447,3 +448,32 @@ def test_binning_mode_mismatch_between_stages_is_safe(cuda):
         assert flags == 0 and torch.equal(img, ref), m
     with pytest.raises(_lib.GGDError):
         _split_frame(lib, s, cuda, 3, 1)
+
+
+def test_clustered_depths_beyond_the_chunked_sort_fall_back_to_radix(cuda):
+    """Tile lists longer than the 24576-word shared-memory buffer are sorted per tile in depth chunks; when one
+    1/128 slice of a list's depth interval alone overflows the buffer (here: every splat at nearly one depth, 16 tiles
+    of ~40k instances) the kernel raises status flag 8 and the binding renders the frame again with the radix sort.
+    The result must be the radix path's bits."""
+    from gaussian_gan_decoder_b200 import rasterizer as rz
+    lib = _lib.load()
+    P, size = 700_000, 64
+    s = synthetic.raster_scene(P, size=size, seed_offset=13)
+    V = s["viewmatrix"]
+    d = V[:3, 2] / V[:3, 2].norm()
+    s["means3D"] = (s["means3D"] - (s["means3D"] @ d)[:, None] * d[None, :]).contiguous()      # one plane facing the camera
+    s = to_dev(s, cuda)
+    rz._binning_hint.pop((cuda.index, P, size, size), None)
+    prev = lib.ggd_raster_binning(1)
+    try:
+        auto = run_ours(s, cuda)
+        st = (C.c_uint32 * 2)()
+        _lib.check(lib.ggd_raster_status(None, C.c_void_p(auto["_buffers"][0].data_ptr()), P, st))
+        lib.ggd_raster_binning(0)
+        radix = run_ours(s, cuda)
+    finally:
+        lib.ggd_raster_binning(prev)
+    counts = auto["ranges"].view(-1, 2)[:, 1] - auto["ranges"].view(-1, 2)[:, 0]
+    assert int(counts.max()) > 24576
+    assert rz._binning_hint[(cuda.index, P, size, size)][0] == 0       # the shape is remembered as radix-only
+    assert_bit_exact(auto, radix, P)
