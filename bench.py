@@ -768,11 +768,16 @@ def run_extra(args, rank, world, dev):
         _lib.check(lib.ggd_raster_binning_info(None, _lib.ptr(out[3]), P5, info))
         st = {n: (round(t[k], 4) if t[k] >= 0 else None) for k, n in enumerate(STAGES)}
         tiles5 = (S5 // 16) ** 2
-        by = {"preprocess": 131 * P5, "duplicate": 20 * P5 + 12 * R5, "sort": 152 * R5, "ranges": 8 * R5 + 8 * tiles5,
-              "blend": 40 * R5 + 20 * S5 * S5}
+        if info[0]:    # binned per tile (class API: reference-order arrays kept): scatter 20 B/Gaussian + 20 B/instance, tile sort 20 B/instance
+            by = {"preprocess": 131 * P5, "duplicate": 20 * P5 + 20 * R5, "sort": 20 * R5, "ranges": None, "blend": 40 * R5 + 20 * S5 * S5}
+            note = "per-tile path: algorithmic bytes scatter 20 P + 20 R, tile sort 20 R (lists mostly stream through L2 / shared memory)"
+        else:
+            by = {"preprocess": 131 * P5, "duplicate": 20 * P5 + 12 * R5, "sort": 152 * R5, "ranges": 8 * R5 + 8 * tiles5,
+                  "blend": 40 * R5 + 20 * S5 * S5}
+            note = "radix-path algorithmic bytes (sort = 8 + 6 x 24 B per instance)"
         extra.update(stages_ms=st, binning={"per_tile": bool(info[0]), "longest_tile_list": int(info[1])},
                      stages_hbm_gbs={k: hbm_gbs(b, st.get(k)) for k, b in by.items()}, hbm_peak_gbs=peaks()["hbm"],
-                     stages_note="radix-path algorithmic bytes (sort = 8 + 6 x 24 B per instance)")
+                     stages_note=note)
         del first, out
         units, name = 1, "rasterised frames/s @2048^2, 2M trained-like Gaussians (raster only)"
     for i in range(max(args.warmup, 3)):
