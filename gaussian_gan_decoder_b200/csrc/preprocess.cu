@@ -448,7 +448,9 @@ int launch_preprocess(cudaStream_t s, const PreprocessArgs& a, const GeomState& 
     const int blocks = (a.P + kThreads - 1) / kThreads;
     PreprocessArgs b = a;
     const int tiles = a.grid_x * a.grid_y;
-    b.hist_tiles = (a.tile_counts && tiles <= 4096) ? tiles : 0;      // 16 KB of dynamic shared memory at most
+    b.hist_tiles = (a.tile_counts && tiles <= 16384) ? tiles : 0;     // up to 64 KB of dynamic shared memory (2048^2)
+    if (b.hist_tiles > 8192)
+        GGD_CUDA_CHECK(cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
     preprocess_kernel<<<blocks, kThreads, sizeof(uint32_t) * (size_t)b.hist_tiles, s>>>(b, g.depths, radii, g.means2D, g.cov3D,
                                                   g.conic_opacity, g.rgb, g.tiles_touched, g.clamped);
     GGD_LAUNCH_CHECK("preprocess_kernel");

@@ -52,6 +52,11 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+# The reference-order key/value arrays ("point_list_keys_unsorted", "point_list_unsorted": duplicateWithKeys' output) are
+# read by nothing but ggd_raster_field users, i.e. tests and debugging; a frame binned per tile skips writing them
+# (GGD_BINNING_LEAN, 12 bytes per instance) unless this is set.  Everything downstream is unchanged either way.
+keep_reference_order_arrays = False
+
 # instance-count guess per (device, P, H, W): drives the binning-buffer capacity
 _capacity_hint = {}
 _tls = threading.local()
@@ -139,11 +144,12 @@ class _CNamespace:
                         float(scale_modifier), p(rotations), p(cov3D_precomp), p(viewmatrix), p(projmatrix),
                         p(campos), float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
                         p(geom), p(radii), host_R, mode)
+            lean = 0 if keep_reference_order_arrays else _lib.BINNING_LEAN
 
             def render(cap):
                 binning = torch.empty(workspace_sizes(P, W, H, cap)[1], dtype=torch.uint8, device=dev)
                 _lib.check(lib.ggd_raster_render(s, P, W, H, p(background), p(colors), p(radii), p(geom),
-                                                 p(binning), cap, p(img), p(out_color), mode))
+                                                 p(binning), cap, p(img), p(out_color), mode | lean))
                 return binning
 
             _lib.check(lib.ggd_raster_preprocess(*pre_args))

@@ -157,6 +157,7 @@ def run_ours(scene, dev):
     e = torch.empty(0, device=dev)
     g = lambda k: scene[k] if scene.get(k) is not None else e
     P, W, H = scene["means3D"].shape[0], scene["W"], scene["H"]
+    rz.keep_reference_order_arrays = True      # the parity tests compare duplicateWithKeys' output as well
     R, color, radii, geom, binning, img = rz._C.rasterize_gaussians(
         g("bg"), g("means3D"), g("colors_precomp"), g("opacities"), g("scales"), g("rotations"),
         scene.get("scale_modifier", 1.0), g("cov3D_precomp"), g("viewmatrix"), g("projmatrix"),
