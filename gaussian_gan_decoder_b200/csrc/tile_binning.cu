@@ -104,6 +104,12 @@ tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int 
 }
 
 constexpr int kScatterThreads = 256;
+// A CTA whose 256 Gaussians emit at least kScatterDenseMin instances (large splats) claims its places in two levels:
+// it counts its instances per tile in shared memory, reserves its share of every non-empty tile's segment with ONE
+// global atomic per tile, and then hands out the places inside its share with a second shared-memory counter.  With one
+// global atomic per instance a trained-like 512^2 frame sends 6.4 M atomics to 1024 cursors (~3300 per CTA over at most
+// 1024 tiles).  Costs 8 bytes of shared memory per tile; images with more than 4096 tiles take the direct path.
+constexpr uint32_t kScatterDenseMin = 1024;
 
 // Same slot-centric walk as duplicate_kernel (binning.cu): CTA = 256 Gaussians' slot interval, thread =
 // slots s, s+256, ...; additionally to the reference-order key/value arrays (kept for the debug
@@ -114,9 +120,10 @@ tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ me
                     const float* __restrict__ depths, const uint32_t* __restrict__ offsets,
                     const int* __restrict__ radii, uint64_t* __restrict__ keys_unsorted,
                     uint32_t* __restrict__ vals_unsorted, uint64_t* __restrict__ words, uint32_t* __restrict__ cursors,
-                    const uint32_t* __restrict__ counters)
+                    const uint32_t* __restrict__ counters, int hist_tiles)
 {
     if (__ldg(counters + 4) == 0u) return;
+    extern __shared__ uint32_t s_scatter[];   // [hist_tiles] per-tile counts, then bases | [hist_tiles] per-tile ranks handed out
     __shared__ uint32_t s_end[kScatterThreads];
     __shared__ uint32_t s_depth[kScatterThreads];
     __shared__ uint32_t s_rect[kScatterThreads];
@@ -143,19 +150,54 @@ tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ me
     __syncthreads();
     const int last = min(kScatterThreads, P - base) - 1;
     const uint32_t block_end = s_end[last];
-    for (uint32_t s = block_start + t; s < block_end; s += kScatterThreads) {
+    // slot s of this CTA's interval -> (Gaussian g inside the CTA, tile)
+    auto locate = [&](uint32_t s, int& g, uint32_t& tile) {
         int lo = 0, hi = last;
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
             const int mid = (lo + hi) >> 1;
             if (s_end[mid] > s) hi = mid; else lo = mid + 1;
         }
-        const int g = lo;
+        g = lo;
         const uint32_t g_start = (g == 0) ? block_start : s_end[g - 1];
         const uint32_t j = s - g_start;
         const uint32_t w = s_w[g];
         const uint32_t rc = s_rect[g];
-        const uint32_t tile = ((rc >> 16) + j / w) * (uint32_t)grid_x + (rc & 0xffffu) + j % w;
+        tile = ((rc >> 16) + j / w) * (uint32_t)grid_x + (rc & 0xffffu) + j % w;
+    };
+    const uint32_t n_slots = block_end - block_start;
+    if (hist_tiles > 0 && n_slots >= kScatterDenseMin) {
+        uint32_t* s_base = s_scatter;
+        uint32_t* s_rank = s_scatter + hist_tiles;
+        for (int i = t; i < hist_tiles; i += kScatterThreads) { s_base[i] = 0u; s_rank[i] = 0u; }
+        __syncthreads();
+        for (uint32_t k = t; k < n_slots; k += kScatterThreads) {
+            int g; uint32_t tile;
+            locate(block_start + k, g, tile);
+            atomicAdd(&s_base[tile], 1u);
+        }
+        __syncthreads();
+        for (int i = t; i < hist_tiles; i += kScatterThreads) {
+            const uint32_t c = s_base[i];
+            if (c) s_base[i] = atomicAdd(cursors + (size_t)i * kTileCountStride + 2, c);   // the CTA's base in the tile's segment
+        }
+        __syncthreads();
+        for (uint32_t k = t; k < n_slots; k += kScatterThreads) {
+            const uint32_t s = block_start + k;
+            int g; uint32_t tile;
+            locate(s, g, tile);
+            const uint32_t depth = s_depth[g], id = (uint32_t)(base + g);
+            if (kRefOrder) {
+                keys_unsorted[s] = ((uint64_t)tile << 32) | depth;
+                vals_unsorted[s] = id;
+            }
+            words[s_base[tile] + atomicAdd(&s_rank[tile], 1u)] = ((uint64_t)depth << 32) | id;   // any order inside the share
+        }
+        return;
+    }
+    for (uint32_t s = block_start + t; s < block_end; s += kScatterThreads) {
+        int g; uint32_t tile;
+        locate(s, g, tile);
         const uint32_t depth = s_depth[g], id = (uint32_t)(base + g);
         if (kRefOrder) {   // the reference's duplicateWithKeys output (emission order); nothing downstream reads it here
             keys_unsorted[s] = ((uint64_t)tile << 32) | depth;
@@ -618,9 +660,12 @@ int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const Geo
 {
     (void)capacity; (void)im;
     const int blocks = (P + kScatterThreads - 1) / kScatterThreads;
+    const int tiles = grid_x * grid_y;
+    const int hist_tiles = tiles <= 4096 ? tiles : 0;
     auto kern = ref_order_arrays ? tile_scatter_kernel<true> : tile_scatter_kernel<false>;
-    kern<<<blocks, kScatterThreads, 0, s>>>(P, grid_x, grid_y, g.means2D, g.depths, g.point_offsets, radii,
-                                            b.keys_unsorted, b.vals_unsorted, b.keys_tmp, g.tile_counts, g.counters);
+    kern<<<blocks, kScatterThreads, sizeof(uint32_t) * 2 * (size_t)hist_tiles, s>>>(
+        P, grid_x, grid_y, g.means2D, g.depths, g.point_offsets, radii, b.keys_unsorted, b.vals_unsorted, b.keys_tmp,
+        g.tile_counts, g.counters, hist_tiles);
     GGD_LAUNCH_CHECK("tile_scatter_kernel");
     return GGD_OK;
 }
