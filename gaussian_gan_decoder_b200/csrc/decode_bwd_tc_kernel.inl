@@ -113,7 +113,7 @@ decode_bwd_chain_tc_kernel(const DecodeBwdTcArgs args)
                 uint32_t pk[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const __half2 hv = __floats2half2_rn(acc[2 * q] / 3.f, acc[2 * q + 1] / 3.f);
+                    const __half2 hv = __floats2half2_rn(acc[2 * q] * (1.0f / 3.0f), acc[2 * q + 1] * (1.0f / 3.0f));   // rounded to fp16 next: no IEEE division
                     pk[q] = *reinterpret_cast<const uint32_t*>(&hv);
                 }
                 *reinterpret_cast<uint4*>(X0 + canon(pt, 8 * sub, kK0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);

@@ -34,6 +34,73 @@ __device__ __forceinline__ void gelu_block(const uint32_t* v, uint32_t* o)
     o[4 * J + 3] = *reinterpret_cast<const uint32_t*>(&y3);
 }
 
+// Samples the T tiles of a group into their layer-0 operands.  Thread e of the 512 epilogue threads: channel octet
+// e & 3, x tap (e >> 2) & 1, point e >> 3 of a 64-point half tile.  The 6 T (half tile, plane) units of a thread form one
+// software pipeline: the loads of unit u + 1 are issued before unit u is accumulated (two register buffers).
+template <int NZ>
+__device__ __forceinline__ void sample_group(const DecodeFwdArgs& a, uint8_t* base0, uint32_t base_stride, int T, int first_point,
+                                             int e, int k0)
+{
+    const int sub = e & 3, dx = (e >> 2) & 1, row = e >> 3;
+    const size_t plane_bytes = (size_t)a.D * a.H * a.W * kFeat * 2;
+    const char* pl = reinterpret_cast<const char*>(a.planes) + sub * 16;
+    TapColumn<NZ> ta, tb;
+    auto load_xyz = [&](int gp, float (&c)[3]) {   // rows past the end sample the origin; nothing of them is stored
+        c[0] = c[1] = c[2] = 0.f;
+        if (gp < a.P) { c[0] = __ldg(a.xyz + 3 * (size_t)gp); c[1] = __ldg(a.xyz + 3 * (size_t)gp + 1); c[2] = __ldg(a.xyz + 3 * (size_t)gp + 2); }
+    };
+    auto issue = [&](TapColumn<NZ>& t, int p, const float (&c)[3]) {
+        const float x = a.coord_scale * c[0], y = a.coord_scale * c[1], z = a.coord_scale * c[2];
+        // tri-planes: (x,y) (x,z) (z,x); tri-grids: (x,y,z) (x,z,y) (y,z,x) -> (W,H,D)
+        if (NZ == 1) t.issue(pl + p * plane_bytes, 1, a.H, a.W, p == 2 ? z : x, p == 0 ? y : (p == 1 ? z : x), 0.f, dx);
+        else t.issue(pl + p * plane_bytes, a.D, a.H, a.W, p == 2 ? y : x, p == 0 ? y : z, p == 0 ? z : (p == 1 ? y : x), dx);
+    };
+    auto finish = [&](uint8_t* base, int pt, const float (&c)[3], float (&acc)[8]) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], 4);
+        if (dx == 0) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {   // rounded to fp16 next: no IEEE division
+                const __half2 hv = __floats2half2_rn(acc[2 * q] * (1.0f / 3.0f), acc[2 * q + 1] * (1.0f / 3.0f));
+                pk[q] = *reinterpret_cast<const uint32_t*>(&hv);
+            }
+            *reinterpret_cast<uint4*>(base + canon(pt, 8 * sub, k0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        } else if (a.pos_freqs == 0 && sub < 2) {
+            // the rest of the row, k0 = 48: columns 32..39 = [x y z 0 0 0 0 0] (sub 0), 40..47 = [0 .. 0 1] (sub 1); the
+            // chained columns are filled in later by the last-layer epilogues
+            uint4 rest = make_uint4(0u, 0u, 0u, 0x3c000000u);   // fp16 1.0 in the top half of .w
+            if (sub == 0) {
+                const __half2 xy = __floats2half2_rn(c[0], c[1]), z0 = __floats2half2_rn(c[2], 0.f);
+                rest = make_uint4(*reinterpret_cast<const uint32_t*>(&xy), *reinterpret_cast<const uint32_t*>(&z0), 0u, 0u);
+            }
+            *reinterpret_cast<uint4*>(base + canon(pt, kFeat + 8 * sub, k0)) = rest;
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc[q] = 0.f;
+    };
+    float cur[3], nxt[3], acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    load_xyz(first_point + row, cur);
+    issue(ta, 0, cur);
+    for (int i = 0; i < T; ++i) {
+        uint8_t* base = base0 + (uint32_t)i * base_stride;
+        load_xyz(first_point + i * kM + 64 + row, nxt);
+        issue(tb, 1, cur); ta.accumulate(acc);
+        issue(ta, 2, cur); tb.accumulate(acc);
+        issue(tb, 0, nxt); ta.accumulate(acc);
+        finish(base, row, cur, acc);
+        cur[0] = nxt[0]; cur[1] = nxt[1]; cur[2] = nxt[2];
+        const bool more = i + 1 < T;
+        if (more) load_xyz(first_point + (i + 1) * kM + row, nxt);
+        issue(ta, 1, cur); tb.accumulate(acc);
+        issue(tb, 2, cur); ta.accumulate(acc);
+        if (more) issue(ta, 0, nxt);
+        tb.accumulate(acc);
+        finish(base, row + 64, cur, acc);
+        cur[0] = nxt[0]; cur[1] = nxt[1]; cur[2] = nxt[2];
+    }
+}
+
 // Cycle accounting of one CTA's roles (GGD_DECODE_PROF=1 selects the instrumented instantiation; read back with
 // ggd_debug_decode_profile): [0] kernel, [1] epilogue warp 0 sampling, [2] waiting for an accumulator, [3] hidden-layer
 // epilogues, [4] last-layer epilogues, [5] MMA thread waiting for an operand, [6] for weights, [7] issuing.
@@ -83,52 +150,17 @@ decode_tc_kernel(const DecodeFwdArgs a, const int T)
             *reinterpret_cast<uint4*>(smem + sm.ones + canon(r, 0, 16)) = one;
             *reinterpret_cast<uint4*>(smem + sm.ones + canon(r, 8, 16)) = zero;
         }
-        const size_t plane_stride = (size_t)a.D * a.H * a.W * kFeat;
         uint32_t n_acc[kSlots] = {0, 0, 0};
         for (int g = blockIdx.x; g < groups; g += gridDim.x) {
             const long long t_s = now();
-            // ---- sample all T tiles into their layer-0 operands: 4 lanes per point, 128 points per pass ----
+            // ---- sample all T tiles into their layer-0 operands ----
+            if (a.arch == 0) sample_group<1>(a, smem + sm.base0, sm.base_stride, T, g * T * kM, e, k0);
+            else sample_group<2>(a, smem + sm.base0, sm.base_stride, T, g * T * kM, e, k0);
             for (int i = 0; i < T; ++i) {
                 uint8_t* base = smem + sm.base0 + (uint32_t)i * sm.base_stride;
                 const int p0 = (g * T + i) * kM;
-                const int sub = e & 3, pt = e >> 2, gps = p0 + pt;
-                const __half* pl = reinterpret_cast<const __half*>(a.planes);
-                float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                float rx = 0.f, ry = 0.f, rz = 0.f;
-                if (gps < a.P) {
-                    rx = __ldg(a.xyz + 3 * (size_t)gps); ry = __ldg(a.xyz + 3 * (size_t)gps + 1); rz = __ldg(a.xyz + 3 * (size_t)gps + 2);
-                    const float x = a.coord_scale * rx, y = a.coord_scale * ry, z = a.coord_scale * rz;
-                    if (a.arch == 0) {   // (x,y) (x,z) (z,x)
-                        sample8h<1>(pl, 1, a.H, a.W, x, y, 0.f, sub, acc);
-                        sample8h<1>(pl + plane_stride, 1, a.H, a.W, x, z, 0.f, sub, acc);
-                        sample8h<1>(pl + 2 * plane_stride, 1, a.H, a.W, z, x, 0.f, sub, acc);
-                    } else {             // (x,y,z) (x,z,y) (y,z,x) -> (W,H,D)
-                        sample8h<2>(pl, a.D, a.H, a.W, x, y, z, sub, acc);
-                        sample8h<2>(pl + plane_stride, a.D, a.H, a.W, x, z, y, sub, acc);
-                        sample8h<2>(pl + 2 * plane_stride, a.D, a.H, a.W, y, z, x, sub, acc);
-                    }
-                }
-                uint32_t pk[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const __half2 hv = __floats2half2_rn(acc[2 * q] / 3.f, acc[2 * q + 1] / 3.f);
-                    pk[q] = *reinterpret_cast<const uint32_t*>(&hv);
-                }
-                *reinterpret_cast<uint4*>(base + canon(pt, 8 * sub, k0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                // the rest of the row: position (+ embedding), zeroed chain columns, constant one
-                if (a.pos_freqs == 0) {
-                    // k0 = 48: columns 32..39 = [x y z 0 0 0 0 0] (lane sub 0), 40..47 = [0 .. 0 1] (lane sub 1);
-                    // the chained columns are filled in later by the last-layer epilogues
-                    if (sub < 2) {
-                        uint4 row = make_uint4(0u, 0u, 0u, 0x3c000000u);   // fp16 1.0 in the top half of .w
-                        if (sub == 0) {
-                            const __half2 xy = __floats2half2_rn(rx, ry), z0 = __floats2half2_rn(rz, 0.f);
-                            row = make_uint4(*reinterpret_cast<const uint32_t*>(&xy), *reinterpret_cast<const uint32_t*>(&z0), 0u, 0u);
-                        }
-                        *reinterpret_cast<uint4*>(base + canon(pt, kFeat + 8 * sub, k0)) = row;
-                    }
-                    continue;
-                }
+                if (a.pos_freqs == 0) continue;
+                // position + embedding, zeroed chain columns, constant one: one thread per row
                 if (colq != 0) continue;
                 const int gp = p0 + r;
                 float px[3] = {0.f, 0.f, 0.f};

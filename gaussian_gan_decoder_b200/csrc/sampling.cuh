@@ -50,23 +50,34 @@ __device__ __forceinline__ float4 sample4(const float* __restrict__ plane, int a
 
 namespace ggd {
 
-// fp16 channels-last planes, 8 channels (16 bytes) per lane.  All taps of a plane are issued as
-// one batch of independent 16-byte loads (out-of-range taps read a clamped texel with weight 0),
-// so a thread has up to 8 loads in flight instead of a load->FMA chain.
+// fp16 channels-last planes, 8 channels (16 bytes) per lane.  Written for instruction count: bounds are folded into
+// the per-axis weights — an out-of-range tap reads a clamped texel with weight 0 — and the byte offsets are per-axis
+// too, so a tap costs one three-input add, one 16-byte load, a weight product and its 8 conversions + 8 FMAs: ~750
+// instructions for the three tri-grid samples of a point quarter (1300 with per-tap bounds tests and 64-bit index
+// arithmetic), same bits as before.
+// (The mixed-precision FMA of sm_100 — fma.rn.f32.f16, SASS FHFMA — would save the conversions but wants the weight
+// in fp16: measured, the frame against the reference loses 10 dB with trained-like weights.  Not used.)
+// one axis of grid_sample (align_corners=False, zeros padding): weights of the two taps, byte offsets of their texels
+__device__ __forceinline__ void sample_axis(float g, int n, uint32_t stride_bytes, float (&w)[2], uint32_t (&o)[2])
+{
+    const float i = ((g + 1.f) * n - 1.f) * 0.5f, f0 = floorf(i);
+    const int i0 = (int)f0;
+    const float w1 = i - f0, w0 = 1.f - w1;
+    w[0] = (unsigned)i0 < (unsigned)n ? w0 : 0.f;
+    w[1] = (unsigned)(i0 + 1) < (unsigned)n ? w1 : 0.f;
+    o[0] = (uint32_t)min(max(i0, 0), n - 1) * stride_bytes;
+    o[1] = (uint32_t)min(max(i0 + 1, 0), n - 1) * stride_bytes;
+}
 template <int NZ>   // 1: bilinear plane, 2: trilinear grid
 __device__ __forceinline__ void sample8h(const __half* __restrict__ plane, int D, int H, int W,
                                          float gx, float gy, float gz, int c8, float (&acc)[8])
 {
-    const float ix = ((gx + 1.f) * W - 1.f) * 0.5f, iy = ((gy + 1.f) * H - 1.f) * 0.5f;
-    const float fx0 = floorf(ix), fy0 = floorf(iy);
-    const int x0 = (int)fx0, y0 = (int)fy0;
-    const float wx[2] = {1.f - (ix - fx0), ix - fx0}, wy[2] = {1.f - (iy - fy0), iy - fy0};
-    int z0 = 0;
-    float wz[2] = {1.f, 0.f};
-    if (NZ == 2) {
-        const float iz = ((gz + 1.f) * D - 1.f) * 0.5f, fz0 = floorf(iz);
-        z0 = (int)fz0; wz[1] = iz - fz0; wz[0] = 1.f - wz[1];
-    }
+    const char* base = reinterpret_cast<const char*>(plane) + c8 * 16;
+    float wx[2], wy[2], wz[2] = {1.f, 0.f};
+    uint32_t ox[2], oy[2], oz[2] = {0u, 0u};
+    sample_axis(gx, W, kFeat * 2, wx, ox);
+    sample_axis(gy, H, (uint32_t)W * (kFeat * 2), wy, oy);
+    if (NZ == 2) sample_axis(gz, D, (uint32_t)H * W * (kFeat * 2), wz, oz);
     uint4 v[NZ * 4];
     float w[NZ * 4];
 #pragma unroll
@@ -75,12 +86,9 @@ __device__ __forceinline__ void sample8h(const __half* __restrict__ plane, int D
         for (int dy = 0; dy < 2; ++dy)
 #pragma unroll
             for (int dx = 0; dx < 2; ++dx) {
-                const int x = x0 + dx, y = y0 + dy, z = z0 + dz;
-                const bool ok = x >= 0 && x < W && y >= 0 && y < H && z >= 0 && z < D;
-                const int xc = min(max(x, 0), W - 1), yc = min(max(y, 0), H - 1), zc = min(max(z, 0), D - 1);
-                w[(dz * 2 + dy) * 2 + dx] = ok ? wx[dx] * wy[dy] * wz[dz] : 0.f;
-                v[(dz * 2 + dy) * 2 + dx] =
-                    __ldg(reinterpret_cast<const uint4*>(plane + (((size_t)zc * H + yc) * W + xc) * kFeat) + c8);
+                const int t = (dz * 2 + dy) * 2 + dx;
+                w[t] = NZ == 2 ? wx[dx] * wy[dy] * wz[dz] : wx[dx] * wy[dy];
+                v[t] = __ldg(reinterpret_cast<const uint4*>(base + (oz[dz] + oy[dy] + ox[dx])));
             }
 #pragma unroll
     for (int t = 0; t < NZ * 4; ++t) {
@@ -93,6 +101,50 @@ __device__ __forceinline__ void sample8h(const __half* __restrict__ plane, int D
         }
     }
 }
+
+// One x column of a sample, split into "issue the loads" and "use them", so that a caller can keep the next plane's
+// loads in flight while it accumulates the current one (the sampling phase of the tensor-core decoder is bound by
+// memory latency x loads in flight per thread, not by issue, L1 tag lookups or L2 throughput — measured).
+// The two lanes (dx = 0, 1) of a point's channel octet read the two x taps of every (z, y) row — the eight lanes of a
+// point fetch 128 contiguous bytes per row; the caller adds the two lanes' sums.
+template <int NZ>   // 1: bilinear plane, 2: trilinear grid
+struct TapColumn {
+    uint4 v[NZ * 2];
+    float w[NZ * 2];
+    __device__ __forceinline__ void issue(const char* __restrict__ plane_c8 /* plane + 16 * channel octet */, int D, int H, int W,
+                                          float gx, float gy, float gz, int dx)
+    {
+        const float ix = ((gx + 1.f) * W - 1.f) * 0.5f, fx0 = floorf(ix);
+        const int xi = (int)fx0 + dx;
+        const float wx1 = ix - fx0, wxl = dx ? wx1 : 1.f - wx1;
+        const float wx = (unsigned)xi < (unsigned)W ? wxl : 0.f;
+        const char* base = plane_c8 + (uint32_t)min(max(xi, 0), W - 1) * (kFeat * 2);
+        float wy[2], wz[2] = {1.f, 0.f};
+        uint32_t oy[2], oz[2] = {0u, 0u};
+        sample_axis(gy, H, (uint32_t)W * (kFeat * 2), wy, oy);
+        if (NZ == 2) sample_axis(gz, D, (uint32_t)H * W * (kFeat * 2), wz, oz);
+#pragma unroll
+        for (int dz = 0; dz < NZ; ++dz)
+#pragma unroll
+            for (int dy = 0; dy < 2; ++dy) {
+                w[dz * 2 + dy] = NZ == 2 ? wx * wy[dy] * wz[dz] : wx * wy[dy];
+                v[dz * 2 + dy] = __ldg(reinterpret_cast<const uint4*>(base + (oz[dz] + oy[dy])));
+            }
+    }
+    __device__ __forceinline__ void accumulate(float (&acc)[8]) const
+    {
+#pragma unroll
+        for (int t = 0; t < NZ * 2; ++t) {
+            const __half2* h = reinterpret_cast<const __half2*>(&v[t]);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 f = __half22float2(h[q]);
+                acc[2 * q] = fmaf(w[t], f.x, acc[2 * q]);
+                acc[2 * q + 1] = fmaf(w[t], f.y, acc[2 * q + 1]);
+            }
+        }
+    }
+};
 
 }  // namespace ggd
 
