@@ -702,7 +702,8 @@ def run_extra(args, rank, world, dev):
     """Secondary workloads (reported in DESIGN.md / profiles/, not the driver's headline):
     train  = BASELINE configs[3] alone (also a sub-object of the main line)
     views  = BASELINE configs[2]: 64 latents x 8 views at 512^2, latent-major sharding over the ranks
-    hires  = BASELINE configs[4]: 2048^2 raster of 2M trained-like Gaussians (sort / blend bound)"""
+    hires  = BASELINE configs[4]: 2048^2 raster of 2M trained-like Gaussians (sort / blend bound)
+    config0 = BASELINE configs[0]: 100k-point decoder forward on EG3D tri-planes, GPU beside the reference class on the host cores"""
     from gaussian_gan_decoder_b200 import synthetic
     from gaussian_gan_decoder_b200.data_parallel import shard_frames
     from gaussian_gan_decoder_b200.pipeline import FramePipeline
@@ -722,6 +723,55 @@ def run_extra(args, rank, world, dev):
             print(json.dumps(run_train_leg(args, rank, world, dev, sets, device_camera(dev), bg)), flush=True)
         else:
             run_train_leg(args, rank, world, dev, sets, device_camera(dev), bg)
+        return
+    if args.workload == "config0":
+        # BASELINE configs[0]: EG3D tri-planes (3 x 32 x 256^2), ParallelDecoder as the reference constructs it (positional
+        # embedding on), 100k points, decode only.  The generator is out of scope: seeded synthetic planes stand in for
+        # G.synthesis, on both sides.  Timed here: this package on the GPU (tensor-core path, then the exact fp32 path) and
+        # the reference's own class on the host cores (oracle/_ref/pyref; rank 0).
+        from gaussian_gan_decoder_b200.decoder_models import ParallelDecoder
+        P0 = 100_000
+        planes = synthetic.planes("eg3d", synthetic.gen(11), res=256)
+        xyz = synthetic.head_shell_points(P0, synthetic.gen(12))
+        torch.manual_seed(303)
+        dec = ParallelDecoder(synthetic.SyntheticGenerator(planes.to(dev), "eg3d", 1), use_xyz_embedding=True, use_gen_finetune=False, device=dev)
+        z, c, xyz_d = torch.zeros(1, 512, device=dev), torch.zeros(1, 25, device=dev), xyz.to(dev)
+
+        def gpu_ms(precision):
+            dec.precision = precision
+            with torch.no_grad():
+                for _ in range(max(args.warmup, 3)):
+                    dec(z, c, xyz_d, 1.0)
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(args.steps):
+                    dec(z, c, xyz_d, 1.0)
+                e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / args.steps
+        ms16, ms32 = gpu_ms("fp16"), gpu_ms("fp32")
+        cpu = None
+        if rank == 0:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import ref_runtime
+            if ref_runtime.available():
+                ref_runtime.add_paths("eg3d")
+                torch.set_num_threads(os.cpu_count() or 1)
+                rdec = ref_runtime.make_decoder("parallel", "eg3d", 1, planes, "cpu", use_xyz_embedding=True)
+                zc, cc = torch.zeros(1, 512), torch.zeros(1, 25)
+                with torch.no_grad():
+                    rdec(zc, cc, xyz, 1.0)
+                    t0 = time.perf_counter()
+                    n = max(3, min(args.steps, 10))
+                    for _ in range(n):
+                        rdec(zc, cc, xyz, 1.0)
+                    cpu = {"ms": round(1e3 * (time.perf_counter() - t0) / n, 2), "cores": torch.get_num_threads(), "runs": n,
+                           "kind": "reference", "what": "main/decoder_models/parallel_decoder.py (oracle/_ref/pyref, unmodified), torch CPU"}
+            print(json.dumps({"metric": "decoder forwards/s, 100k points, EG3D tri-planes, ParallelDecoder + positional embedding (configs[0], "
+                                        "without G.synthesis: generator out of scope, synthetic planes)",
+                              "value": round(1e3 / ms16, 2), "unit": "1/s", "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+                              "ms_per_step": round(ms16, 4), "higher_is_better": True, "scaling": "weak", "data": "synthetic", "dtype": "fp16",
+                              "config": {"workload": "config0", "points": P0, "fp32_path_ms": round(ms32, 4), "cpu_reference": cpu}}), flush=True)
         return
     if args.workload == "views":
         pairs = shard_frames(64, 8, rank, world, "latent")
@@ -813,7 +863,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ref_cuda"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
-    ap.add_argument("--workload", default="frame", choices=["frame", "train", "views", "hires"])
+    ap.add_argument("--workload", default="frame", choices=["frame", "train", "views", "hires", "config0"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

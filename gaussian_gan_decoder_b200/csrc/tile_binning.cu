@@ -498,23 +498,48 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         const uint32_t tile = __ldg(tile_list + (size_t)li * kTileCountStride + 1);
         const uint2 range = ranges[tile];
         const uint32_t n = range.y - range.x;
-        const uint64_t* src = words + range.x;
+        const uint64_t* gsrc = words + range.x;
+        const bool staged = n <= kLargeStagedMax;
+        uint64_t* s_in = s_out + kLargeStagedMax;
+        // One pass over the list: a thread's words are fetched kWalk at a time BEFORE any of them is used.  The passes
+        // below update shared memory (atomics) per word; written as load-use-load-use a streamed list cost one L2 round
+        // trip per word and thread — 17 to 24 in a row for the 2048^2 frame's lists — instead of three.
+        constexpr int kWalk = 8;
+        auto walk = [&](auto&& use) {
+            for (uint32_t i0 = t; i0 < n; i0 += kWalk * kLargeThreads) {
+                uint64_t w[kWalk];
+#pragma unroll
+                for (int k = 0; k < kWalk; ++k) {
+                    const uint32_t i = i0 + (uint32_t)k * kLargeThreads;
+                    w[k] = i < n ? (staged ? s_in[i] : __ldg(gsrc + i)) : 0ull;
+                }
+#pragma unroll
+                for (int k = 0; k < kWalk; ++k)
+                    if (i0 + (uint32_t)k * kLargeThreads < n) use(w[k]);
+            }
+        };
         // depth interval of the list
         uint32_t dmin = 0xffffffffu, dmax = 0u;
-        if (n <= kLargeStagedMax) {
-            uint64_t* s_in = s_out + kLargeStagedMax;
-            for (uint32_t i = t; i < n; i += kLargeThreads) {
-                const uint64_t w = __ldg(src + i);
-                s_in[i] = w;
-                const uint32_t d = (uint32_t)(w >> 32);
-                dmin = min(dmin, d); dmax = max(dmax, d);
+        if (staged) {
+            for (uint32_t i0 = t; i0 < n; i0 += kWalk * kLargeThreads) {
+                uint64_t w[kWalk];
+#pragma unroll
+                for (int k = 0; k < kWalk; ++k) {
+                    const uint32_t i = i0 + (uint32_t)k * kLargeThreads;
+                    w[k] = i < n ? __ldg(gsrc + i) : 0ull;
+                }
+#pragma unroll
+                for (int k = 0; k < kWalk; ++k) {
+                    const uint32_t i = i0 + (uint32_t)k * kLargeThreads;
+                    if (i < n) {
+                        s_in[i] = w[k];
+                        const uint32_t d = (uint32_t)(w[k] >> 32);
+                        dmin = min(dmin, d); dmax = max(dmax, d);
+                    }
+                }
             }
-            src = s_in;      // generic pointer into shared memory from here on (made visible by the barrier below)
         } else {
-            for (uint32_t i = t; i < n; i += kLargeThreads) {
-                const uint32_t d = (uint32_t)(src[i] >> 32);
-                dmin = min(dmin, d); dmax = max(dmax, d);
-            }
+            walk([&](uint64_t w) { const uint32_t d = (uint32_t)(w >> 32); dmin = min(dmin, d); dmax = max(dmax, d); });
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -527,7 +552,7 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         for (int k = 0; k < kLargeThreads / 32; ++k) { dmin = min(dmin, s_red[0][k]); dmax = max(dmax, s_red[1][k]); }
         const float scale_c = (float)kCoarse / ((float)(dmax - dmin) + 1.0f);
         auto coarse_of = [&](uint64_t w) { return min((uint32_t)(kCoarse - 1), (uint32_t)((float)((uint32_t)(w >> 32) - dmin) * scale_c)); };
-        for (uint32_t i = t; i < n; i += kLargeThreads) atomicAdd(&s_c[coarse_of(src[i])], 1u);
+        walk([&](uint64_t w) { atomicAdd(&s_c[coarse_of(w)], 1u); });
         __syncthreads();
         coarse_scan(s_c, s_cstart);
         __syncthreads();
@@ -550,15 +575,14 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
                 // The chunk is still copied out (unsorted) so that the kernels queued behind this one read valid indices.
                 if (t == 0) { atomicOr(status_flags, 8u); s_nbig = 0; }
                 __syncthreads();
-                for (uint32_t i = t; i < n; i += kLargeThreads) {
-                    const uint64_t w = src[i];
+                walk([&](uint64_t w) {
                     const uint32_t kc = coarse_of(w);
                     if (kc >= c0 && kc < c1) {
                         const uint32_t pos = atomicAdd(&s_nbig, 1u);
                         vals[range.x + first + pos] = (uint32_t)w;
                         keys[range.x + first + pos] = ((uint64_t)tile << 32) | (w >> 32);
                     }
-                }
+                });
                 __syncthreads();
                 c0 = c1;
                 continue;
@@ -574,11 +598,11 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
                 const float below = (float)(s_cstart[kc] - first), in_bin = (float)(s_cstart[kc + 1] - s_cstart[kc]);
                 return min(kLargeBuckets - 1u, (uint32_t)((below + (x - (float)kc) * in_bin) * ratio));
             };
-            for (uint32_t i = t; i < n; i += kLargeThreads) {
+            walk([&](uint64_t w) {
                 uint32_t kc;
-                const uint32_t bk = bucket(src[i], kc);
+                const uint32_t bk = bucket(w, kc);
                 if (whole || (kc >= c0 && kc < c1)) atomicAdd(&s_hist[bk], 1u);
-            }
+            });
             __syncthreads();
             // exclusive scan; thread t owns buckets [t kPer, (t + 1) kPer)
             uint32_t cnt[kPer], sum = 0;
@@ -600,12 +624,11 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
                 for (int q = 0; q < kPer; ++q) { s_hist[t * kPer + q] = run; run += cnt[q]; }
             }
             __syncthreads();
-            for (uint32_t i = t; i < n; i += kLargeThreads) {
-                const uint64_t w = src[i];
+            walk([&](uint64_t w) {
                 uint32_t kc;
                 const uint32_t bk = bucket(w, kc);
                 if (whole || (kc >= c0 && kc < c1)) s_out[atomicAdd(&s_hist[bk], 1u)] = w;
-            }
+            });
             __syncthreads();
             {
                 uint32_t b0 = start;
