@@ -79,6 +79,32 @@ def test_vs_cpu_oracle_config_shapes(cuda, arch, variant, posenc, P, precision):
     check(out, ref, precision)
 
 
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("arch,variant", [("panohead", "sequential_reverse"), ("eg3d", "parallel")])
+def test_points_outside_and_on_the_border_of_the_planes(cuda, arch, variant, precision):
+    """grid_sample(padding_mode="zeros", align_corners=False) at and beyond the planes' border: points up to 1.5x outside
+    the box, points exactly on the faces / corners, and points within one texel of them (taps with one, two or three
+    out-of-range coordinates).  head_shell_points never leaves the inner 60 % of the box."""
+    g = synthetic.gen(23)
+    depth = 3 if arch == "panohead" else 1
+    res = 64
+    planes = synthetic.planes(arch, g, res=res, depth=depth)
+    wide = (torch.rand(20_000, 3, generator=g) - 0.5) * 1.5                    # coordinate scale 2: up to +-1.5
+    t = 1.0 / res                                                              # one texel in box units is 1 / res
+    edge = torch.tensor([-0.5, -0.5 + 0.25 * t, -0.5 + 0.5 * t, -0.5 + t, 0.0, 0.5 - t, 0.5 - 0.5 * t, 0.5 - 0.25 * t, 0.5,
+                         -0.5 - 0.25 * t, 0.5 + 0.25 * t, 0.5 + 0.75 * t, -0.5 - 0.75 * t])
+    grid = torch.cartesian_prod(edge, edge, edge)
+    xyz = torch.cat([wide, grid]).contiguous()
+    torch.manual_seed(6)
+    dec = CLASSES[variant](StubG(planes.to(cuda), arch, depth), use_xyz_embedding=False, use_gen_finetune=False, device=cuda)
+    dec.precision = precision
+    flat = torch.cat([p.detach().reshape(-1).cpu() for p in dec.get_params_custom()])
+    with torch.no_grad():
+        out = dec.decode(planes.to(cuda), xyz.to(cuda))
+        ref = do.decode(arch, variant, 0, flat, planes, xyz, 1.0, depth)
+    check(out, ref, precision)
+
+
 def test_state_dict_keys_match_reference_names(cuda):
     dec = SequentialDecoderReverse(StubG(torch.zeros(1, 3, 32, 8, 8)), use_xyz_embedding=False, device=cuda)
     keys = [k for k in dec.state_dict().keys() if not k.startswith("G.")]
