@@ -65,6 +65,22 @@ def test_vs_reference_cuda_backward(cuda, P, size, fov, trained):
 
 
 @pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("W,H", [(200, 120), (90, 250)])
+def test_non_square_images_backward(cuda, W, H):
+    P = 3000
+    s = to_dev(synthetic.raster_scene(P, size=max(W, H), fov_deg=14.0, seed_offset=W + H), cuda)
+    s["W"], s["H"] = W, H
+    gen = torch.Generator(device="cpu"); gen.manual_seed(W * H)
+    dL = torch.randn(3, H, W, generator=gen).to(cuda)
+    ref = RefCuda()
+    ref.forward(s, cuda)
+    gr = ref.backward(dL, cuda)
+    go = ours_backward(s, dL, cuda)
+    for n in NAMES:
+        close(go[n], gr[n], n)
+
+
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
 def test_sh_degree3_and_precomputed_inputs(cuda):
     P = 4000
     base = to_dev(synthetic.raster_scene(P, size=160, seed_offset=5), cuda)

@@ -76,6 +76,21 @@ def test_bit_exact_vs_reference_cuda(cuda, P, size, fov, trained):
 
 
 @pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("W,H", [(200, 120), (120, 200), (333, 17), (16, 250)])
+def test_bit_exact_non_square_images(cuda, W, H):
+    """image_width != image_height (the settings carry both; every scene above is square): the same matrices with another
+    pixel grid are a distorted but valid camera for both implementations."""
+    s = synthetic.raster_scene(3000, size=max(W, H), fov_deg=14.0, seed_offset=W + H)
+    s = to_dev(s, cuda)
+    s["W"], s["H"] = W, H
+    ref = RefCuda().forward(s, cuda)
+    ours = run_ours(s, cuda)
+    assert ref["R"] > 0
+    assert_bit_exact(ours, ref, 3000)
+    assert ours["out_color"].shape == (3, H, W)
+
+
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
 def test_bit_exact_full_size_config2(cuda):
     """BASELINE config 2 shape: 500k Gaussians, 512x512 — both attribute distributions."""
     for trained in (False, True):
