@@ -217,6 +217,24 @@ def test_alternative_inputs_bit_exact(cuda):
     assert torch.equal(ours["clamped"].view(P, 3)[vis], ref["clamped"].view(P, 3)[vis])
 
 
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("scale_modifier", [0.6, 1.7])
+@pytest.mark.parametrize("deg,M", [(0, 16), (1, 4), (1, 16), (2, 9), (2, 16)])
+def test_scale_modifier_and_partial_sh_degrees(cuda, scale_modifier, deg, M):
+    """GaussianRasterizationSettings.scale_modifier != 1 (the viewers' splat-size slider) and an active SH degree below
+    the stored one (3DGS raises it during training), as well as M = (deg + 1)^2 exactly."""
+    P = 3000
+    s = to_dev(synthetic.raster_scene(P, size=144, seed_offset=int(10 * scale_modifier) + deg + M), cuda)
+    g = synthetic.gen(100 + deg + M)
+    s["shs"] = (0.3 * torch.randn(P, M, 3, generator=g)).to(cuda)
+    s["sh_degree"] = deg
+    s["scale_modifier"] = scale_modifier
+    ref = RefCuda().forward(s, cuda)
+    ours = run_ours(s, cuda)
+    assert ref["R"] > 0
+    assert_bit_exact(ours, ref, P)
+
+
 def test_capacity_overflow_recovers(cuda):
     from gaussian_gan_decoder_b200 import rasterizer as rz
     s = to_dev(synthetic.raster_scene(20000, size=256, seed_offset=3), cuda)
