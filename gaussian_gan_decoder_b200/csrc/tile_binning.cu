@@ -506,12 +506,16 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         // trip per word and thread — 17 to 24 in a row for the 2048^2 frame's lists — instead of three.
         constexpr int kWalk = 8;
         auto walk = [&](auto&& use) {
+            if (staged) {      // the list sits in shared memory: nothing to batch
+                for (uint32_t i = t; i < n; i += kLargeThreads) use(s_in[i]);
+                return;
+            }
             for (uint32_t i0 = t; i0 < n; i0 += kWalk * kLargeThreads) {
                 uint64_t w[kWalk];
 #pragma unroll
                 for (int k = 0; k < kWalk; ++k) {
                     const uint32_t i = i0 + (uint32_t)k * kLargeThreads;
-                    w[k] = i < n ? (staged ? s_in[i] : __ldg(gsrc + i)) : 0ull;
+                    w[k] = i < n ? __ldg(gsrc + i) : 0ull;
                 }
 #pragma unroll
                 for (int k = 0; k < kWalk; ++k)

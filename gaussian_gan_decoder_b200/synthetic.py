@@ -42,11 +42,14 @@ def trained_like_attributes(P, g):
 
 
 def activated(attrs):
-    """GaussianModel getters (gaussian_splatting/scene/gaussian_model.py:99-121)."""
+    """GaussianModel getters (gaussian_splatting/scene/gaussian_model.py:99-121), as seeded INPUT data: evaluated in float64
+    and rounded once.  torch's vectorised fp32 exp / sigmoid on the CPU may differ in the last bit between its vector body
+    and scalar tail, i.e. with the alignment of the tensor, i.e. from one process to the next — and one splat whose radius
+    changes by a pixel changes the instance count of a "fixed" benchmark scene (seen: R = 6 438 932 vs 6 438 940)."""
     return dict(
-        scales=torch.exp(attrs["scale"]),
-        rotations=torch.nn.functional.normalize(attrs["rotation"]),
-        opacities=torch.sigmoid(attrs["opacity"]),
+        scales=torch.exp(attrs["scale"].double()).float(),
+        rotations=torch.nn.functional.normalize(attrs["rotation"].double()).float(),
+        opacities=torch.sigmoid(attrs["opacity"].double()).float(),
         shs=attrs["color"][:, None, :].contiguous(),
     )
 
