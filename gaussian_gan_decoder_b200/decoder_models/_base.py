@@ -18,8 +18,9 @@ class FusedDecoderBase(nn.Module):
 
     def __init__(self, G, hidden_dim=128, use_xyz_embedding=True, use_gen_finetune=True, device="cuda"):
         super().__init__()
-        if hidden_dim != 128:
-            raise NotImplementedError("the fused sm_100a kernels are specialised for hidden_dim=128")
+        if not 1 <= int(hidden_dim) <= fused.KERNEL_HIDDEN:
+            raise NotImplementedError(f"hidden_dim={hidden_dim}: the fused sm_100a kernels are {fused.KERNEL_HIDDEN} units wide; narrower "
+                                      "decoders run zero-padded on them, wider ones are not supported")
         self.hidden_dim = hidden_dim
         self.use_xyz_embedding = use_xyz_embedding
         self.use_gen_finetune = use_gen_finetune
@@ -80,7 +81,7 @@ class FusedDecoderBase(nn.Module):
             if planes.shape[2] != 32 * depth:
                 raise ValueError(f"feature_planes has {planes.shape[2]} channels, expected 32*{depth}")
             self._cfg_cache[key] = fused.make_config(arch, self.VARIANT, depth, planes.shape[-2], planes.shape[-1],
-                                                     10 if self.use_xyz_embedding else 0, self.hidden_dim,
+                                                     10 if self.use_xyz_embedding else 0, fused.KERNEL_HIDDEN,
                                                      kw["box_warp"], self.SCALE_BIAS, precision)
         return self._cfg_cache[key]
 

@@ -21,6 +21,11 @@ PRECISIONS = {"fp32": 0, "fp16": 1}
 # "fp16": tcgen05 tensor-core kernel (fp16 operands, fp32 accumulation) — the production path.
 # "fp32": exact CUDA-core kernel — the accuracy anchor.  Overridable per decoder (``.precision``).
 DEFAULT_PRECISION = os.environ.get("GGD_DECODE_PRECISION", "fp16")
+# Width the kernels are specialised for (tile N = 128, TMEM column budget).  A narrower decoder (--hidden_dim < 128 in the
+# reference's training script) runs on the same kernels with its weights zero-padded into the 128-wide layout: the padded
+# hidden units compute gelu(0) = 0 — exactly, in the erf, tanh and polynomial forms alike — and feed zero weights, so the
+# function and every gradient of a real parameter are those of the narrow network; gradients of padded entries are 0.
+KERNEL_HIDDEN = 128
 
 
 def make_config(arch, variant, depth, h, w, pos_freqs, hidden, box_warp, scale_bias, precision="fp32"):
@@ -73,21 +78,31 @@ class FlatParams:
                 yield hi, li, 0, lin.weight
                 yield hi, li, 1, lin.bias
 
+    def view_of(self, buf, hi, li, is_b, t):
+        """The part of ``buf`` (a flat buffer in the ggd.h layout) that belongs to parameter ``t``: the whole block for a
+        128-wide decoder, its leading rows / columns — a strided view — for a narrower one (see KERNEL_HIDDEN)."""
+        off, fi, fo = param_offset(self.cfg, hi, li, is_b)
+        if is_b:
+            return buf[off:off + fo][:t.shape[0]]
+        return buf[off:off + fo * fi].view(fo, fi)[:t.shape[0], :t.shape[1]]
+
     def adopt(self, owner):
         first = next(self._tensors(owner))[3]
         dev = first.device
-        flat = torch.empty(self.count, dtype=torch.float32, device=dev)
+        hidden = int(getattr(owner, "hidden_dim", KERNEL_HIDDEN))
+        flat = torch.zeros(self.count, dtype=torch.float32, device=dev)      # zeros: the padding of a narrow decoder
         grad = torch.zeros(self.count, dtype=torch.float32, device=dev)
+        narrow = lambda d: hidden if d == KERNEL_HIDDEN else d
         with torch.no_grad():
             for hi, li, is_b, t in self._tensors(owner):
                 off, fi, fo = param_offset(self.cfg, hi, li, is_b)
-                shape = (fo,) if is_b else (fo, fi)
+                shape = (narrow(fo),) if is_b else (narrow(fo), narrow(fi))
                 if tuple(t.shape) != shape:
                     raise ValueError(f"{HEADS[hi]}_decoder layer {li}: expected {shape}, got {tuple(t.shape)}")
-                view = flat[off:off + t.numel()].view(shape)
+                view = self.view_of(flat, hi, li, is_b, t)
                 view.copy_(t.detach().to(torch.float32))
                 t.data = view
-                t.grad = grad[off:off + t.numel()].view(shape)
+                t.grad = self.view_of(grad, hi, li, is_b, t)
         self.flat, self.flat_grad = flat, grad
         self._params = [t for _, _, _, t in self._tensors(owner)]
         self._packed_version = None

@@ -35,8 +35,7 @@ class _FusedDecode(torch.autograd.Function):
         owner._flat.last_dflat = dflat
         grads = []
         for hi, li, is_b, t in owner._flat._tensors(owner):
-            off, fi, fo = fused.param_offset(owner._flat.cfg, hi, li, is_b)
-            grads.append(dflat[off:off + t.numel()].view_as(t))
+            grads.append(owner._flat.view_of(dflat, hi, li, is_b, t))
         return (None, dplanes, None, *grads)
 
 

@@ -26,10 +26,22 @@ def forward(decoder, triplane_features, gaussian_features):
     if P == 0:
         return out
     lin = decoder.linears()
+    H, K = decoder.hidden_dim, 128
+    if H > K:
+        raise NotImplementedError(f"hidden_dim={H}: the kernel is {K} units wide")
+    if H == K and all(l.weight.is_contiguous() and l.bias.is_contiguous() for l in lin):
+        w = [(l.weight, l.bias) for l in lin]
+    else:       # a narrower head (or one whose parameters are strided views of a padded buffer): zero-padded copies
+        def pad(t, *shape):
+            out = torch.zeros(*shape, dtype=torch.float32, device=dev)
+            out[tuple(slice(0, n) for n in t.shape)] = t.detach()
+            return out
+        w = [(pad(lin[0].weight, K, decoder.n_features), pad(lin[0].bias, K)), (pad(lin[1].weight, K, K), pad(lin[1].bias, K)),
+             (pad(lin[2].weight, K, K), pad(lin[2].bias, K)), (pad(lin[3].weight, decoder.out_features, K), lin[3].bias.detach().contiguous())]
     p = _lib.ptr
     with torch.cuda.device(dev):
         _lib.check(lib.ggd_mlp_forward(C.c_void_p(torch.cuda.current_stream().cuda_stream), p(tri), p(gf), k, P,
-                                       p(lin[0].weight), p(lin[0].bias), p(lin[1].weight), p(lin[1].bias),
-                                       p(lin[2].weight), p(lin[2].bias), p(lin[3].weight), p(lin[3].bias),
-                                       decoder.hidden_dim, decoder.out_features, p(out)))
+                                       p(w[0][0]), p(w[0][1]), p(w[1][0]), p(w[1][1]),
+                                       p(w[2][0]), p(w[2][1]), p(w[3][0]), p(w[3][1]),
+                                       K, decoder.out_features, p(out)))
     return out

@@ -160,10 +160,8 @@ class TrainPipeline:
         """``.grad`` of the 40 parameters = views of the flat gradient buffer (set once; optimizer.step reads them)."""
         if getattr(self, "_grads_of", None) is flat.flat_grad:
             return
-        from .decoder_models import fused
         for hi, li, is_b, t in flat._tensors(self.dec):
-            off, _, _ = fused.param_offset(flat.cfg, hi, li, is_b)
-            t.grad = flat.flat_grad[off:off + t.numel()].view_as(t)
+            t.grad = flat.view_of(flat.flat_grad, hi, li, is_b, t)
         self._grads_of = flat.flat_grad
 
     def _allreduce(self, buf):

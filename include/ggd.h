@@ -257,7 +257,8 @@ typedef struct ggd_decoder_config {
     int plane_depth;   /* triplane_depth D (1 for EG3D)                                       */
     int plane_h, plane_w;
     int pos_freqs;     /* 0 = raw xyz, 10 = Embedder(num_freqs=10) -> 63 dims                 */
-    int hidden;        /* must be 128 (the width the kernels are specialised for)             */
+    int hidden;        /* must be 128, the width the kernels are specialised for; the host classes run a
+                          narrower decoder by zero-padding its weights into this layout              */
     float box_warp;
     float scale_bias;  /* activate_scale offset: -2 (parallel, sequential), -2.5 (reverse)    */
     int precision;     /* 0 = fp32 CUDA-core path (max-abs 1e-3 contract),

@@ -96,10 +96,10 @@ def mlp(flat, layout, head, x):
     return x
 
 
-def decode(arch, variant, pos_freqs, flat, planes, xyz, box_warp=1.0, depth=1):
+def decode(arch, variant, pos_freqs, flat, planes, xyz, box_warp=1.0, depth=1, hidden=128):
     """Returns the reference's result dict (raw attributes) plus the activated tensors the
-    rasteriser receives."""
-    layout, _ = flat_layout(variant, pos_freqs)
+    rasteriser receives.  ``hidden``: the reference's --hidden_dim (flat holds the true, unpadded shapes)."""
+    layout, _ = flat_layout(variant, pos_freqs, hidden)
     feat = sample_from_planes(arch, planes, xyz, box_warp, depth).mean(0)   # [P,32]
     info = embed(xyz, pos_freqs)
     res = {}

@@ -91,7 +91,7 @@ VARIANT_CLASS = {"parallel": "ParallelDecoder", "sequential": "SequentialDecoder
                  "sequential_reverse": "SequentialDecoderReverse"}
 
 
-def make_decoder(variant, arch, depth, planes, device, use_xyz_embedding=False, seed=303):
+def make_decoder(variant, arch, depth, planes, device, use_xyz_embedding=False, seed=303, hidden_dim=128):
     """An instance of the reference's decoder class (call ``add_paths(arch, ...)`` first).  Default nn.Linear
     initialisation under ``seed``; NOTE the reference constructs its five heads in its own order, so the random
     stream differs from the product classes — copy parameters with ``load_flat`` for like-for-like runs."""
@@ -107,7 +107,7 @@ def make_decoder(variant, arch, depth, planes, device, use_xyz_embedding=False, 
         persistence._check_pickleable = lambda obj: None
     torch.manual_seed(seed)
     G = StubG(planes, arch, depth, generate_planes().to(device))
-    dec = getattr(mod, VARIANT_CLASS[variant])(G, hidden_dim=128, use_xyz_embedding=use_xyz_embedding,
+    dec = getattr(mod, VARIANT_CLASS[variant])(G, hidden_dim=hidden_dim, use_xyz_embedding=use_xyz_embedding,
                                               use_gen_finetune=False, device=device)
     dec.triplane_sr = "None"
     return dec

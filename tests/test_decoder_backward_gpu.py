@@ -49,13 +49,23 @@ def test_gradients_with_points_outside_the_planes(cuda, arch, variant, precision
     _check_gradients(cuda, arch, variant, False, points, 32, precision, synthetic.gen(29), q=5e-3)
 
 
-def _check_gradients(cuda, arch, variant, posenc, make_xyz, res, precision, g, q=3e-3):
+@pytest.mark.parametrize("arch,variant,posenc,hidden", [("panohead", "sequential_reverse", False, 64), ("eg3d", "parallel", True, 40)])
+@pytest.mark.parametrize("precision", ["fp32", "fp16"])
+def test_gradients_of_a_narrow_decoder(cuda, arch, variant, posenc, hidden, precision):
+    """hidden_dim < 128: gradients arrive in the parameters' own (reference) shapes; against autograd through the oracle
+    evaluated at the true width."""
+    _check_gradients(cuda, arch, variant, posenc, lambda g: synthetic.head_shell_points(2000, g) * 1.5, 32, precision,
+                     synthetic.gen(37), hidden=hidden)
+
+
+def _check_gradients(cuda, arch, variant, posenc, make_xyz, res, precision, g, q=3e-3, hidden=128):
     depth = 3 if arch == "panohead" else 1
     planes = synthetic.planes(arch, g, res=res, depth=depth)
     xyz = make_xyz(g)
     P = xyz.shape[0]
     torch.manual_seed(11)
-    dec = CLASSES[variant](StubG(planes.to(cuda), arch, depth), use_xyz_embedding=posenc, use_gen_finetune=True, device=cuda)
+    dec = CLASSES[variant](StubG(planes.to(cuda), arch, depth), hidden_dim=hidden, use_xyz_embedding=posenc, use_gen_finetune=True,
+                           device=cuda)
     dec.precision = precision
     douts = {h: torch.randn(P, n, generator=g) for h, n in zip(HEADS, (3, 3, 4, 1, 3))}
 
@@ -70,10 +80,10 @@ def _check_gradients(cuda, arch, variant, posenc, make_xyz, res, precision, g, q
     # oracle + autograd on CPU
     flat = torch.cat([p.detach().reshape(-1).cpu() for p in dec.get_params_custom()[:40]]).requires_grad_(True)
     plr = planes.clone().requires_grad_(True)
-    ref = do.decode(arch, variant, 10 if posenc else 0, flat, plr, xyz, 1.0, depth)
+    ref = do.decode(arch, variant, 10 if posenc else 0, flat, plr, xyz, 1.0, depth, hidden=hidden)
     sum((ref[h] * douts[h]).sum() for h in HEADS).backward()
 
-    layout, _ = do.flat_layout(variant, 10 if posenc else 0)
+    layout, _ = do.flat_layout(variant, 10 if posenc else 0, hidden)
     for h, l, kind, off, shape in layout:
         n = 1
         for d in shape:

@@ -24,10 +24,10 @@ TIGHT = {"fp32": 5e-5, "fp16": 5e-4}
 PRECISIONS = ["fp32", "fp16"]
 
 
-def check(out, ref, precision):
+def check(out, ref, precision, tight=TIGHT):
     for h in HEADS:
         err = (out[h].cpu() - ref[h]).abs().max().item()
-        assert err <= TOL and err <= TIGHT[precision], (h, precision, err)
+        assert err <= TOL and err <= tight[precision], (h, precision, err)
         if ref[h].shape[0] >= 100:      # "relative" is relative to the attribute's range: needs a population, not one point
             assert err <= 1e-2 * ref[h].abs().max().item(), (h, precision, err)
 
@@ -103,6 +103,49 @@ def test_points_outside_and_on_the_border_of_the_planes(cuda, arch, variant, pre
         out = dec.decode(planes.to(cuda), xyz.to(cuda))
         ref = do.decode(arch, variant, 0, flat, planes, xyz, 1.0, depth)
     check(out, ref, precision)
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("arch,variant,posenc,hidden", [("panohead", "sequential_reverse", False, 64), ("eg3d", "parallel", True, 100),
+                                                          ("eg3d", "sequential", False, 8)])
+def test_hidden_dim_below_128(cuda, arch, variant, posenc, hidden, precision):
+    """--hidden_dim < 128 (main/train_pano2gaussian_decoder.py:48, base_decoder.py:9): the parameters have the reference's
+    shapes; the kernels read them zero-padded to their own width.  Against the oracle evaluated at the TRUE width."""
+    g = synthetic.gen(31)
+    depth = 3 if arch == "panohead" else 1
+    planes = synthetic.planes(arch, g, res=64, depth=depth)
+    xyz = synthetic.head_shell_points(5000, g)
+    torch.manual_seed(8)
+    dec = CLASSES[variant](StubG(planes.to(cuda), arch, depth), hidden_dim=hidden, use_xyz_embedding=posenc, use_gen_finetune=False,
+                           device=cuda)
+    dec.precision = precision
+    lin = dec.color_decoder.linears()
+    assert tuple(lin[0].weight.shape) == (hidden, dec.color_decoder.n_features) and tuple(lin[1].weight.shape) == (hidden, hidden)
+    assert tuple(lin[3].weight.shape) == (3, hidden) and tuple(lin[2].bias.shape) == (hidden,)
+    with torch.no_grad():
+        out = dec.decode(planes.to(cuda), xyz.to(cuda))
+        flat = torch.cat([p.detach().reshape(-1).cpu() for p in dec.get_params_custom()])
+        ref = do.decode(arch, variant, 10 if posenc else 0, flat, planes, xyz, 1.0, depth, hidden=hidden)
+    # nn.Linear's default init of a narrow layer is wider (+-1/sqrt(hidden)), and so are the activations: the fp16 path
+    # gets the contract's bounds (1e-3 absolute, 1e-2 of the range) instead of the 128-wide decoders' measured 5e-4
+    tight = {"fp32": TIGHT["fp32"], "fp16": TOL}
+    check(out, ref, precision, tight)
+    # a parameter update through the views (what an optimizer does) is seen, and the padding stays zero
+    with torch.no_grad():
+        for p in dec.get_params_custom():
+            p.mul_(1.05)
+        out = dec.decode(planes.to(cuda), xyz.to(cuda))
+        flat = torch.cat([p.detach().reshape(-1).cpu() for p in dec.get_params_custom()])
+        ref = do.decode(arch, variant, 10 if posenc else 0, flat, planes, xyz, 1.0, depth, hidden=hidden)
+    check(out, ref, precision, tight)
+    true_sum = sum(float(p.detach().abs().double().sum()) for p in dec.get_params_custom())
+    assert abs(float(dec._flat.flat.abs().double().sum()) - true_sum) <= 1e-6 * true_sum
+
+
+def test_hidden_dim_above_kernel_width_is_refused(cuda):
+    planes = synthetic.planes("eg3d", synthetic.gen(1), res=16)
+    with pytest.raises(NotImplementedError, match="128 units wide"):
+        ParallelDecoder(StubG(planes.to(cuda), "eg3d", 1), hidden_dim=256, device=cuda)
 
 
 def test_state_dict_keys_match_reference_names(cuda):

@@ -175,3 +175,31 @@ def test_reference_decoder_class_vs_decoder_models(cuda, ref_modules, precision,
         b = ref_renderer.render_simple(cam, ref_runtime.gaussian_model_from(got), bg_color=bg)["render"]
     mse = float(((a - b) ** 2).mean())
     assert 10 * math.log10(1.0 / max(mse, 1e-20)) >= 50.0
+
+
+def test_reference_decoder_with_another_hidden_dim_loads_and_agrees(cuda, ref_modules):
+    """A decoder trained with --hidden_dim 64 (main/train_pano2gaussian_decoder.py:48): the reference class's state_dict
+    loads into this package's class of the same width, and the two agree (fp32 path)."""
+    from gaussian_gan_decoder_b200.decoder_models import SequentialDecoderReverse
+    P, H = 20_000, 64
+    g = synthetic.gen(41)
+    planes = synthetic.planes("panohead", g, res=64, depth=3).to(cuda)
+    xyz = synthetic.head_shell_points(P, g).to(cuda)
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        ref_dec = ref_runtime.make_decoder("sequential_reverse", "panohead", 3, planes, cuda, hidden_dim=H)
+        dec = SequentialDecoderReverse(StubG(planes, "panohead", 3), hidden_dim=H, use_xyz_embedding=False, use_gen_finetune=False,
+                                       device=cuda)
+        sd = {k: v for k, v in ref_dec.state_dict().items() if not k.startswith("G.")}
+        res = dec.load_state_dict(sd, strict=False)
+        assert not [k for k in res.missing_keys if not k.startswith("G.")] and not res.unexpected_keys
+        z, c = torch.zeros(1, 512, device=cuda), torch.zeros(1, 25, device=cuda)
+        for precision, tol in (("fp32", 2e-5), ("fp16", 5e-4)):
+            dec.precision = precision
+            with torch.no_grad():
+                want, got = ref_dec(z, c, xyz, 1.0), dec(z, c, xyz, 1.0)
+            for h in HEADS:
+                assert float((want[h] - got[h]).abs().max()) <= tol, (h, precision)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old

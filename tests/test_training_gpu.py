@@ -45,13 +45,14 @@ def _setup(cuda, seed, P=20_000, res=32, size=128):
     return planes, xyz, cam, bg
 
 
-def _decoder(planes, cuda, seed=1):
+def _decoder(planes, cuda, seed=1, hidden=128):
     torch.manual_seed(seed)
-    return SequentialDecoderReverse(StubG(planes, "panohead", 3), use_xyz_embedding=False, use_gen_finetune=False, device=cuda)
+    return SequentialDecoderReverse(StubG(planes, "panohead", 3), hidden_dim=hidden, use_xyz_embedding=False, use_gen_finetune=False,
+                                    device=cuda)
 
 
-@pytest.mark.parametrize("mode", ["target", "dL_dimage"])
-def test_train_pipeline_matches_autograd_route(cuda, mode):
+@pytest.mark.parametrize("mode,hidden", [("target", 128), ("dL_dimage", 128), ("target", 48)])
+def test_train_pipeline_matches_autograd_route(cuda, mode, hidden):
     """TrainPipeline (pre-allocated buffers, C ABI end to end, no autograd, no host sync inside a step) takes the same
     optimisation step as ``training_step`` (decoder classes + GaussianModel + render_simple under autograd): compared
     through the parameters after one SGD step, i.e. through the full flat gradient.  Tolerance: the backward sums are
@@ -62,7 +63,7 @@ def test_train_pipeline_matches_autograd_route(cuda, mode):
     target = torch.full((3, 128, 128), 0.3, device=cuda)
     dimg = torch.randn(3, 128, 128, generator=synthetic.gen(7)).to(cuda)
     kw = dict(target=target) if mode == "target" else dict(dL_dimage=dimg)
-    a, b = _decoder(planes, cuda), _decoder(planes, cuda)
+    a, b = _decoder(planes, cuda, hidden=hidden), _decoder(planes, cuda, hidden=hidden)
     a._ensure_flat(planes), b._ensure_flat(planes)
     before = a._flat.flat.clone()
     assert torch.equal(before, b._flat.flat)
@@ -78,6 +79,9 @@ def test_train_pipeline_matches_autograd_route(cuda, mode):
     assert float((ga - gb).abs().max()) <= 1e-3 * scale, (float((ga - gb).abs().max()), scale)
     assert abs(float(loss_a) - float(tp.loss)) <= 1e-4 * max(1.0, abs(float(loss_a)))
     assert b._flat.in_sync(b)
+    if hidden < 128:      # the zero padding of a narrow decoder took no step
+        true = sum(float(p.detach().abs().double().sum()) for p in b.get_params_custom())
+        assert abs(float(b._flat.flat.abs().double().sum()) - true) <= 1e-6 * true
 
 
 def test_train_pipeline_reduces_loss_and_recovers_from_overflow(cuda):
