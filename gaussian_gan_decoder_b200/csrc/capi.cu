@@ -219,6 +219,7 @@ int ggd_raster_preprocess(void* stream, int P, int D, int M, int W, int H,
     PreprocessArgs a;
     a.tile_counts = binning ? g.tile_counts : nullptr;
     a.counts_valid = g.counters + 12;
+    a.diff_used = g.counters + 13;
     a.P = P; a.D = D; a.M = shs ? M : 0; a.W = W; a.H = H;
     a.means3D = means3D; a.shs = shs; a.colors_precomp = colors_precomp; a.opacities = opacities;
     a.scales = scales; a.scale_modifier = scale_modifier; a.rotations = rotations;
@@ -269,7 +270,7 @@ int ggd_raster_render(void* stream, int P, int W, int H, const float* background
     {
         StageScope t(s, kStDuplicate);
         if (per_tile) {   // writes every range, picks the path for this frame (counters[4])
-            if (int e = launch_tile_scan(s, g, im, tiles, bin_capacity, P, !radix)) return e;
+            if (int e = launch_tile_scan(s, g, im, grid_x, grid_y, bin_capacity, P, !radix)) return e;
             if (int e = launch_tile_scatter(s, P, grid_x, grid_y, g, radii, b, im, bin_capacity, !lean)) return e;
         } else {
             GGD_CUDA_CHECK(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)tiles, s));

@@ -87,10 +87,12 @@ struct GeomState {
                               // [4] 1 = this frame is binned per tile (tile_binning.cu), [5] longest tile list,
                               // [6] element count the radix kernels see, [7] number of tile lists > kTileSortMax,
                               // [8], [10] tile queues of the blend kernels, [12] 1 = preprocess counted tile_counts
-                              // for this frame (so stage 2 never trusts counts that were not written)
+                              // for this frame (so stage 2 never trusts counts that were not written), [13] 1 = part of
+                              // the counts sits in the difference array (word 3 of the tile records)
     uint64_t* scan_status;    // [scan tiles] decoupled look-back words of the scan
     uint32_t* tile_counts;    // [tiles][kTileCountStride] word 0: instances per tile, counted by preprocess; word 2: the
-                              // tile's write cursor; word 1 of entry i: id of the i-th long tile list.  One 128-byte
+                              // tile's write cursor; word 1 of entry i: id of the i-th long tile list; word 3: 2-D
+                              // difference array of the large rectangles (+1 / -1 at their corners).  One 128-byte
                               // line per tile so the atomics spread over the L2 slices (last field: size depends on W, H)
     size_t bytes;
 };
@@ -139,6 +141,8 @@ struct PreprocessArgs {
     uint32_t* tile_counts;   // optional [grid_x * grid_y][32]: word 0 += 1 for every tile a splat touches
     uint32_t* counts_valid;  // set to 1 by the kernel when tile_counts were written (GeomState::counters[12])
     int hist_tiles;          // set by launch_preprocess: size of the CTA-local tile histogram (0 = none)
+    uint32_t* diff_used;     // GeomState::counters[13]: set when a large rectangle was counted through the difference array
+    int diff_ok;             // set by launch_preprocess: tile_scan_kernel can undo a difference array of this grid
 };
 int launch_preprocess(cudaStream_t s, const PreprocessArgs& a, const GeomState& g, int* radii);
 int launch_scan(cudaStream_t s, int P, const GeomState& g);
@@ -153,7 +157,8 @@ constexpr uint32_t kTileCountStride = 32;  // words between two tiles' counters
 constexpr uint32_t kTileSortMax = 4096;   // longest tile list the register-resident shared-memory sort takes
 constexpr uint32_t kTileSortLargeMax = 24576;   // words the one-CTA-per-SM variant sorts at once (192 KB of words + 32 KB of buckets)
 constexpr uint32_t kTileSortHugeMax = 4 * kTileSortLargeMax;   // longest list of the per-tile path: sorted in depth chunks of <= kTileSortLargeMax
-int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int tiles, uint64_t capacity, int P, bool strict);
+int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int grid_x, int grid_y, uint64_t capacity, int P, bool strict);
+constexpr int kTileDiffMaxTiles = 16384;   // largest grid whose difference array tile_scan_kernel sums in shared memory (2048^2)
 int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g, const int* radii,
                         const BinState& b, const ImgState& im, uint64_t capacity, bool ref_order_arrays);
 int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, const ImgState& im, int tiles);

@@ -23,6 +23,7 @@ namespace ggd {
 namespace {
 
 constexpr int kThreads = 256;
+constexpr uint32_t kRectDiffMin = 32;   // tile rectangles from this size on are counted through the difference array
 
 struct M3 {  // column-major 3x3, m[col][row]
     float m[3][3];
@@ -288,6 +289,24 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
     // histogram first and flushes one atomic per non-empty tile (~3x fewer, each carrying a count).  The choice is per
     // CTA, from its own splats.
     if (a.tile_counts) {
+        // A rectangle of kRectDiffMin tiles or more is not counted tile by tile: it adds +1 / -1 at its four corners to a
+        // 2-D difference array (word 3 of the tile records) and tile_scan_kernel turns that array into per-tile counts with
+        // one 2-D prefix sum over the tile grid — O(1) per splat instead of O(area).  The 2048^2 / 2 M frame touches 140
+        // tiles per Gaussian: 2.8e8 counter updates (0.9 of the kernel's 1.0 ms) become 8e6.
+        const bool big = a.diff_ok && my_tiles >= kRectDiffMin;
+        if (big) {
+            uint32_t* D = a.tile_counts + 3;
+            const uint32_t gx = (uint32_t)a.grid_x;
+            atomicAdd(D + (size_t)(my_rmin.y * gx + my_rmin.x) * 32, 1u);
+            if (my_rmax.x < gx) atomicAdd(D + (size_t)(my_rmin.y * gx + my_rmax.x) * 32, 0xffffffffu);
+            if (my_rmax.y < (uint32_t)a.grid_y) {
+                atomicAdd(D + (size_t)(my_rmax.y * gx + my_rmin.x) * 32, 0xffffffffu);
+                if (my_rmax.x < gx) atomicAdd(D + (size_t)(my_rmax.y * gx + my_rmax.x) * 32, 1u);
+            }
+            *a.diff_used = 1u;          // same value from everyone
+            my_rmax.y = my_rmin.y;      // nothing left for the loops below
+            my_tiles = 0;
+        }
         const bool dense = a.hist_tiles > 0 && __syncthreads_count(my_tiles > 4u) >= kThreads / 2;
         if (dense) {
             for (int i = t; i < a.hist_tiles; i += kThreads) s_cnt[i] = 0u;
@@ -448,7 +467,10 @@ int launch_preprocess(cudaStream_t s, const PreprocessArgs& a, const GeomState& 
     const int blocks = (a.P + kThreads - 1) / kThreads;
     PreprocessArgs b = a;
     const int tiles = a.grid_x * a.grid_y;
-    b.hist_tiles = (a.tile_counts && tiles <= 16384) ? tiles : 0;     // up to 64 KB of dynamic shared memory (2048^2)
+    b.diff_ok = (a.tile_counts && tiles <= kTileDiffMaxTiles) ? 1 : 0;
+    // CTA-local histogram of the small rectangles: 16 KB at most (with the large ones on the difference array the
+    // 64 KB histogram a 2048^2 image used to get only cost occupancy)
+    b.hist_tiles = (a.tile_counts && tiles <= (b.diff_ok ? 4096 : 16384)) ? tiles : 0;
     if (b.hist_tiles > 8192)
         GGD_CUDA_CHECK(cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
     preprocess_kernel<<<blocks, kThreads, sizeof(uint32_t) * (size_t)b.hist_tiles, s>>>(b, g.depths, radii, g.means2D, g.cov3D,

@@ -35,14 +35,46 @@ namespace {
 constexpr int kScanThreadsT = 1024;
 
 __global__ void __launch_bounds__(kScanThreadsT)
-tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int tiles, uint32_t capacity,
+tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int grid_x, int grid_y, uint32_t capacity,
                  const uint32_t* __restrict__ offsets, int P, uint32_t* __restrict__ counters, int strict)
 {
+    extern __shared__ uint32_t s_diff[];   // [tiles] when the grid has at most kTileDiffMaxTiles tiles
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_max, s_carry, s_large;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int tiles = grid_x * grid_y;
+    // Large rectangles were counted as +1 / -1 at their corners (preprocess, word 3 of the tile records): a 2-D inclusive
+    // prefix sum of that array is their per-tile count.  Rows by warps (shuffle scan, 32 columns at a time), then columns
+    // by threads (consecutive threads on consecutive banks).  Arithmetic is modulo 2^32, the sums are counts.
+    const bool diff = counters[13] != 0u;
+    if (diff) {
+        for (int i = t; i < tiles; i += kScanThreadsT) s_diff[i] = counts[(size_t)i * kTileCountStride + 3];
+        __syncthreads();
+        for (int r = warp; r < grid_y; r += kScanThreadsT / 32) {
+            uint32_t carry = 0;
+            for (int x0 = 0; x0 < grid_x; x0 += 32) {
+                const int x = x0 + lane;
+                uint32_t v = x < grid_x ? s_diff[r * grid_x + x] : 0u;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+                    if (lane >= o) v += n;
+                }
+                v += carry;
+                if (x < grid_x) s_diff[r * grid_x + x] = v;
+                carry = __shfl_sync(0xffffffffu, v, 31);
+            }
+        }
+        __syncthreads();
+        for (int c = t; c < grid_x; c += kScanThreadsT) {
+            uint32_t run = 0;
+            for (int y = 0; y < grid_y; ++y) { run += s_diff[y * grid_x + c]; s_diff[y * grid_x + c] = run; }
+        }
+        __syncthreads();
+    }
+    auto count_of = [&](int i) { return counts[(size_t)i * kTileCountStride] + (diff ? s_diff[i] : 0u); };
     uint32_t mx = 0;
-    for (int i = t; i < tiles; i += kScanThreadsT) mx = max(mx, counts[(size_t)i * kTileCountStride]);
+    for (int i = t; i < tiles; i += kScanThreadsT) mx = max(mx, count_of(i));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     if (lane == 0) s_warp[warp] = mx;
@@ -73,7 +105,7 @@ tile_scan_kernel(uint32_t* __restrict__ counts, uint2* __restrict__ ranges, int 
     }
     for (int base = 0; base < tiles; base += kScanThreadsT) {
         const int i = base + t;
-        const uint32_t v = i < tiles ? counts[(size_t)i * kTileCountStride] : 0u;
+        const uint32_t v = i < tiles ? count_of(i) : 0u;
         uint32_t incl = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -674,10 +706,13 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
 
 }  // namespace
 
-int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int tiles, uint64_t capacity, int P, bool strict)
+int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int grid_x, int grid_y, uint64_t capacity, int P, bool strict)
 {
-    tile_scan_kernel<<<1, kScanThreadsT, 0, s>>>(g.tile_counts, im.ranges, tiles, (uint32_t)capacity, g.point_offsets, P,
-                                                 g.counters, strict ? 1 : 0);
+    const int tiles = grid_x * grid_y;
+    const size_t smem = tiles <= kTileDiffMaxTiles ? sizeof(uint32_t) * (size_t)tiles : 0;   // larger grids: preprocess does not use the array
+    if (smem > 48 * 1024) GGD_CUDA_CHECK(cudaFuncSetAttribute(tile_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tile_scan_kernel<<<1, kScanThreadsT, smem, s>>>(g.tile_counts, im.ranges, grid_x, grid_y, (uint32_t)capacity, g.point_offsets, P,
+                                                    g.counters, strict ? 1 : 0);
     GGD_LAUNCH_CHECK("tile_scan_kernel");
     return GGD_OK;
 }
