@@ -235,6 +235,25 @@ def test_scale_modifier_and_partial_sh_degrees(cuda, scale_modifier, deg, M):
     assert_bit_exact(ours, ref, P)
 
 
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("spread,size", [(1.5, 256), (2.5, 192)])
+def test_bit_exact_elongated_rotated_splats(cuda, spread, size):
+    """The blend skips (8x4 pixel block, instance) pairs whose pixels all fall below alpha = 1/255 — decided from the splat's
+    box and, for larger splats, from the minimum of its quadratic form over the block.  Needle-like, rotated splats are
+    where that test has to be conservative: per-axis log-scales N(-5, spread) give axis ratios beyond 100:1 (the most
+    ill-conditioned ones take the 'never culled' branch).  Image, T and contributor counts must keep the reference's bits."""
+    P = 20_000
+    s = synthetic.raster_scene(P, size=size, fov_deg=14.0, seed_offset=int(10 * spread))
+    g = synthetic.gen(500 + int(10 * spread))
+    s["scales"] = torch.exp(-5.0 + spread * torch.randn(P, 3, generator=g)).clamp(max=0.5)
+    s["opacities"] = torch.sigmoid(1.0 + 2.5 * torch.randn(P, 1, generator=g))
+    s = to_dev(s, cuda)
+    ref = RefCuda().forward(s, cuda)
+    ours = run_ours(s, cuda)
+    assert ref["R"] > 10 * P
+    assert_bit_exact(ours, ref, P)
+
+
 def test_capacity_overflow_recovers(cuda):
     from gaussian_gan_decoder_b200 import rasterizer as rz
     s = to_dev(synthetic.raster_scene(20000, size=256, seed_offset=3), cuda)
