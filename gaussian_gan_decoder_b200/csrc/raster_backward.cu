@@ -11,36 +11,16 @@
 //  * the nine per-pair contributions are first summed over the 32 pixels of a warp with
 //    shuffles and over the 8 warps of the tile in shared memory; global memory sees nine
 //    atomics per (tile, Gaussian) instead of nine per (pixel, Gaussian);
-//  * warps skip instances whose conservative footprint misses their 8x4 pixel block, and
+//  * warps skip instances whose conservative footprint misses their 8x4 pixel block (footprint.cuh), and
 //    the replay starts at the tile's largest n_contrib instead of the end of the list;
 //  * the two per-Gaussian kernels of the reference are one kernel.
 #include "common.cuh"
+#include "footprint.cuh"
 
 namespace ggd {
 namespace {
 
 constexpr int kBatch = kTilePixels;
-
-// same conservative footprint test as the forward blend (blend.cu)
-__device__ __forceinline__ uint32_t warp_block_mask(float x, float y, float a, float b, float c, float o,
-                                                    float tile_x0, float tile_y0)
-{
-    if (!(o >= 1.0f / 255.0f)) return (o == o) ? 0u : 0xffu;
-    const float det = a * c - b * b, tr = a + c;
-    if (!(det > 0.f) || !(tr * tr <= 1000.f * det) || !(o <= 1e30f)) return 0xffu;
-    const float s = 2.02f * logf(255.0f * o) + 1e-4f;
-    const float inv = 1.0f / det;
-    const float rx = sqrtf(s * c * inv) * 1.005f + 1e-3f, ry = sqrtf(s * a * inv) * 1.005f + 1e-3f;
-    const float lx0 = x - rx - tile_x0, lx1 = x + rx - tile_x0, ly0 = y - ry - tile_y0, ly1 = y + ry - tile_y0;
-    if (!(lx0 == lx0) || !(lx1 == lx1) || !(ly0 == ly0) || !(ly1 == ly1)) return 0xffu;
-    uint32_t m = 0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) {
-        const float bx0 = (float)((w & 1) * 8), by0 = (float)((w >> 1) * 4);
-        if (lx1 >= bx0 && lx0 <= bx0 + 7.f && ly1 >= by0 && ly0 <= by0 + 3.f) m |= 1u << w;
-    }
-    return m;
-}
 
 __device__ __forceinline__ float warp_sum(float v)
 {
