@@ -1,7 +1,8 @@
 """Decoder backward (chain kernel + tcgen05 weight-gradient GEMMs) against PyTorch autograd
 through the CPU oracle (= the reference's ATen ops).  Gradients are float sums with fp16-staged
-operands for the weight gradients: per tensor, max error <= 2e-2 of the tensor's max magnitude
-and 99 % of the elements within 3e-3 of it."""
+operands for the weight gradients: per tensor, max error <= 6e-3 of the tensor's max magnitude
+and 99 % of the elements within 3e-3 of it (measured on B200, worst over all cases: 3.1e-3 / 2.4e-3 on the
+fp16 path, 2.4e-3 / 1.6e-3 on the fp32 path; every run writes gpurun_out/decoder_backward_errors.json)."""
 import os
 import sys
 
@@ -20,12 +21,27 @@ CLASSES = {"parallel": ParallelDecoder, "sequential": SequentialDecoder, "sequen
 HEADS = ("xyz", "scale", "rotation", "opacity", "color")
 
 
-def close(a, b, name, mx=2e-2, q=3e-3):
+MEASURED = {}      # worst relative errors seen per test, written to gpurun_out/decoder_backward_errors.json
+
+
+def close(a, b, name, mx=6e-3, q=3e-3):
     a, b = a.reshape(-1).double().cpu(), b.reshape(-1).double().cpu()
     scale = b.abs().max().item() + 1e-30
     err = (a - b).abs() / scale
+    q99 = torch.quantile(err[:1_000_000], 0.99).item()
+    case = os.environ.get("PYTEST_CURRENT_TEST", "?").split("::")[-1].split(" ")[0]
+    m = MEASURED.setdefault(case, {"max": 0.0, "q99": 0.0})
+    m["max"], m["q99"] = max(m["max"], err.max().item()), max(m["q99"], q99)
+    try:
+        import json
+        out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "decoder_backward_errors.json"), "w") as f:
+            json.dump(MEASURED, f, indent=1)
+    except OSError:
+        pass
     assert err.max().item() <= mx, (name, err.max().item())
-    assert torch.quantile(err[:1_000_000], 0.99).item() <= q, (name, torch.quantile(err[:1_000_000], 0.99).item())
+    assert q99 <= q, (name, q99)
 
 
 @pytest.mark.parametrize("arch,variant,posenc,P,res", [("eg3d", "parallel", False, 1000, 32), ("panohead", "sequential_reverse", False, 777, 24),
@@ -44,9 +60,9 @@ def test_gradients_with_points_outside_the_planes(cuda, arch, variant, precision
         wide = (torch.rand(3000, 3, generator=g) - 0.5) * 1.5
         edge = torch.tensor([-0.5, -0.5 + 0.25 / 32, 0.0, 0.5 - 0.25 / 32, 0.5, 0.5 + 0.5 / 32, -0.5 - 0.5 / 32])
         return torch.cat([wide, torch.cartesian_prod(edge, edge, edge)]).contiguous()
-    # 99 % bound a little wider than the module's 3e-3: a third of these samples contribute nothing, so the sums the
-    # fp16-staged operands are compared against are smaller
-    _check_gradients(cuda, arch, variant, False, points, 32, precision, synthetic.gen(29), q=5e-3)
+    # 99 % bound a little wider than the module's 3e-3 (measured 2.4e-3): a third of these samples contribute nothing, so
+    # the sums the fp16-staged operands are compared against are smaller
+    _check_gradients(cuda, arch, variant, False, points, 32, precision, synthetic.gen(29), q=4e-3)
 
 
 @pytest.mark.parametrize("arch,variant,posenc,hidden", [("panohead", "sequential_reverse", False, 64), ("eg3d", "parallel", True, 40)])
@@ -89,7 +105,7 @@ def _check_gradients(cuda, arch, variant, posenc, make_xyz, res, precision, g, q
         for d in shape:
             n *= d
         close(ours[off:off + n], flat.grad[off:off + n], f"{h}.{l}.{kind}", q=q)
-    close(ours_planes, plr.grad, "planes", mx=2e-2, q=q)
+    close(ours_planes, plr.grad, "planes", q=q)
 
 
 def test_flat_gradient_buffer_and_no_grad_path(cuda):
