@@ -164,6 +164,24 @@ class PackedPlanes:
     def dim(self):
         return len(self.shape)
 
+    @classmethod
+    def from_host(cls, planes_nchw, pin=True):
+        """The producer for planes that live on the HOST (a cache of per-identity planes, a data loader): fp32
+        ``[1, 3, 32*D, H, W]`` in the generator's layout -> the kernel's layout, built with torch CPU ops, same bytes as
+        ``ggd_planes_channels_last`` writes on the device (round-to-nearest-even fp16, channel index c*D + d as in
+        PanoHead/training/volumetric_rendering/renderer.py:51-52).  Upload it with ``.to(device, non_blocking=True)``:
+        half the bytes of the fp32 planes and no repack kernel per frame."""
+        if planes_nchw.dim() != 5 or planes_nchw.shape[0] != 1 or planes_nchw.shape[1] != 3 or planes_nchw.shape[2] % 32:
+            raise ValueError(f"feature_planes must be [1,3,32*D,H,W], got {tuple(planes_nchw.shape)}")
+        _, _, cd, h, w = planes_nchw.shape
+        d = cd // 32
+        x = planes_nchw.detach().to("cpu", torch.float32).view(3, 32, d, h, w)          # channel = c * D + d
+        packed = x.permute(0, 2, 3, 4, 1).contiguous().to(torch.float16)                    # [3][D][H][W][32]
+        data = packed.view(torch.uint8).reshape(-1)
+        if pin and torch.cuda.is_available():
+            data = data.pin_memory()
+        return cls(data, planes_nchw.shape)
+
     def to(self, device, non_blocking=False):
         return PackedPlanes(self.data.to(device, non_blocking=non_blocking), self.shape)
 

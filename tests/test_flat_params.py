@@ -66,3 +66,17 @@ def test_state_dict_of_a_narrow_decoder_round_trips():
 def test_wider_than_the_kernels_is_refused():
     with pytest.raises(NotImplementedError):
         ParallelDecoder(StubG(torch.zeros(1, 3, 32, 8, 8), "eg3d", 1), hidden_dim=129, device="cpu")
+
+
+def test_packed_planes_host_producer_layout():
+    """PackedPlanes.from_host: [1,3,32*D,H,W] fp32 -> [3][D][H][W][32] fp16, generator channel c*D + d -> (d, c)."""
+    from gaussian_gan_decoder_b200.decoder_models.fused import PackedPlanes
+    D, H, W = 3, 4, 5
+    x = torch.arange(3 * 32 * D * H * W, dtype=torch.float32).view(1, 3, 32 * D, H, W) / 64.0
+    pk = PackedPlanes.from_host(x, pin=False)
+    assert pk.shape == (1, 3, 32 * D, H, W) and pk.data.dtype == torch.uint8 and pk.data.numel() == x.numel() * 2
+    got = pk.data.view(torch.float16).view(3, D, H, W, 32)
+    for (p, d, y, xx, c) in [(0, 0, 0, 0, 0), (2, 1, 3, 4, 31), (1, 2, 2, 1, 7)]:
+        assert got[p, d, y, xx, c] == x[0, p, c * D + d, y, xx].to(torch.float16)
+    with pytest.raises(ValueError):
+        PackedPlanes.from_host(torch.zeros(1, 3, 30, 4, 4))

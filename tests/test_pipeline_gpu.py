@@ -82,6 +82,10 @@ def test_packed_planes_handshake(cuda):
     xyz_g = xyz.clone().requires_grad_(False)
     with pytest.raises(RuntimeError):
         dec(z, c, xyz_g, 1.0)                                    # parameters require grad and grad mode is on
+    # the host-side producer writes the same bytes as the device kernel
+    from gaussian_gan_decoder_b200.decoder_models.fused import PackedPlanes
+    made_on_host = PackedPlanes.from_host(planes.cpu())
+    assert made_on_host.shape == packed.shape and torch.equal(made_on_host.data, packed.data.cpu())
 
 
 def test_pipeline_recovers_when_a_frame_stops_qualifying(cuda):
