@@ -240,6 +240,173 @@ tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ me
     }
 }
 
+// ---- two-level scatter for large images --------------------------------------------------------------------------------
+// With 16 384 tiles (2048^2) and ~140 tiles per Gaussian the scatter above sends 2.8e8 atomics to the tiles' cursors and is
+// bound by the L2 atomic rate (3.4 ms, 8 % of the issue slots used).  Here Gaussians are first binned by SUPER-TILE
+// (kSuper x kSuper tiles, ~6 per Gaussian: 1.2e7 list entries), then a CTA takes a chunk of one super-tile's list, counts its
+// instances per tile in shared memory (64 counters), reserves the chunk's share of each tile's segment with ONE global
+// atomic per tile and hands out the places with a second shared-memory counter: ~4e5 global atomics per frame.
+// The pair lists live in BinState::vals_tmp (scratch of the radix sort, unused on this path; pairs <= instances <= capacity);
+// the super-tiles' counters are words 4-6 of the first tile records.  Any order inside a tile's segment is fine: the tile
+// sort orders by (depth, Gaussian index).
+constexpr int kSuper = 8;                      // tiles per super-tile edge
+constexpr int kSuperMax = 1024;                // super-tiles a CTA-local histogram holds
+constexpr int kSuperThreads = 256;
+constexpr uint32_t kSuperChunk = 1024;         // list entries per unit of work of the emit kernel
+
+__device__ __forceinline__ bool super_rect(const float2* __restrict__ means2D, const int* __restrict__ radii, int idx, int grid_x,
+                                           int grid_y, uint2& rmin, uint2& rmax)
+{
+    const int r = __ldg(radii + idx);
+    if (r <= 0) return false;
+    tile_rect(__ldg(means2D + idx), r, grid_x, grid_y, rmin, rmax);
+    return rmax.x > rmin.x && rmax.y > rmin.y;
+}
+
+// pass 1 (kCount) counts the (Gaussian, super-tile) pairs per super-tile; pass 2 writes the Gaussian ids into the lists
+template <bool kCount>
+__global__ void __launch_bounds__(kSuperThreads)
+super_bin_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ means2D, const int* __restrict__ radii,
+                 uint32_t* __restrict__ recs, uint32_t* __restrict__ list, const uint32_t* __restrict__ counters)
+{
+    if (__ldg(counters + 4) == 0u) return;
+    __shared__ uint32_t s_cnt[kSuperMax], s_rank[kSuperMax];
+    const int t = threadIdx.x, idx = blockIdx.x * kSuperThreads + t;
+    const int sgx = (grid_x + kSuper - 1) / kSuper, ns = sgx * ((grid_y + kSuper - 1) / kSuper);
+    for (int i = t; i < ns; i += kSuperThreads) { s_cnt[i] = 0u; s_rank[i] = 0u; }
+    __syncthreads();
+    uint2 rmin, rmax;
+    const bool live = idx < P && super_rect(means2D, radii, idx, grid_x, grid_y, rmin, rmax);
+    uint32_t sx0 = 0, sx1 = 0, sy0 = 0, sy1 = 0;
+    if (live) { sx0 = rmin.x / kSuper; sx1 = (rmax.x - 1) / kSuper + 1; sy0 = rmin.y / kSuper; sy1 = (rmax.y - 1) / kSuper + 1; }
+    for (uint32_t sy = sy0; sy < sy1; ++sy)
+        for (uint32_t sx = sx0; sx < sx1; ++sx) atomicAdd(&s_cnt[sy * sgx + sx], 1u);
+    __syncthreads();
+    for (int i = t; i < ns; i += kSuperThreads) {
+        const uint32_t c = s_cnt[i];
+        if (c) s_cnt[i] = atomicAdd(recs + (size_t)i * kTileCountStride + (kCount ? 4 : 6), c);   // count, or the CTA's base from the cursor
+    }
+    if (kCount) return;
+    __syncthreads();
+    for (uint32_t sy = sy0; sy < sy1; ++sy)
+        for (uint32_t sx = sx0; sx < sx1; ++sx) {
+            const uint32_t st = sy * sgx + sx;
+            list[s_cnt[st] + atomicAdd(&s_rank[st], 1u)] = (uint32_t)idx;
+        }
+}
+
+// exclusive scan of the super-tiles' counts -> list starts (word 5) and write cursors (word 6); the counts go back to zero
+// so that stage 2 can run again on the same geometry state; counters[14] = number of pairs
+__global__ void __launch_bounds__(kSuperMax)
+super_scan_kernel(int ns, uint32_t* __restrict__ recs, uint32_t* __restrict__ counters)
+{
+    if (counters[4] == 0u) return;
+    __shared__ uint32_t s_warp[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t v = t < ns ? recs[(size_t)t * kTileCountStride + 4] : 0u;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t off = 0;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+    if (t < ns) {
+        recs[(size_t)t * kTileCountStride + 4] = 0u;
+        recs[(size_t)t * kTileCountStride + 5] = off + incl - v;
+        recs[(size_t)t * kTileCountStride + 6] = off + incl - v;
+    }
+    if (t == kSuperMax - 1) counters[14] = off + incl;
+}
+
+// Visits the tiles [x0, x1) x [y0, y1) row by row.  (The large splats of a chunk cover the same tiles, so the lanes of a warp
+// mostly visit the same tile in the same step: same-address shared-memory atomics are merged by the hardware, and the words
+// of a step land next to each other in that tile's segment.  Starting every lane at a different tile was measured: slower,
+// and so was claiming four places before storing the first word.)
+template <typename F>
+__device__ __forceinline__ void walk_rect(uint32_t x0, uint32_t x1, uint32_t y0, uint32_t y1, F&& visit)
+{
+    for (uint32_t ty = y0; ty < y1; ++ty)
+        for (uint32_t tx = x0; tx < x1; ++tx) visit(tx, ty);
+}
+
+template <bool kRefOrder>
+__global__ void __launch_bounds__(kSuperThreads, 8)
+super_emit_kernel(int grid_x, int grid_y, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                  const uint32_t* __restrict__ offsets, const int* __restrict__ radii, uint64_t* __restrict__ keys_unsorted,
+                  uint32_t* __restrict__ vals_unsorted, uint64_t* __restrict__ words, uint32_t* __restrict__ recs,
+                  const uint32_t* __restrict__ list, const uint32_t* __restrict__ counters)
+{
+    if (__ldg(counters + 4) == 0u) return;
+    __shared__ uint32_t s_start[kSuperMax + 1];
+    __shared__ uint32_t s_cnt[kSuper * kSuper], s_rank[kSuper * kSuper];
+    const int t = threadIdx.x;
+    const int sgx = (grid_x + kSuper - 1) / kSuper, ns = sgx * ((grid_y + kSuper - 1) / kSuper);
+    const uint32_t pairs = __ldg(counters + 14);
+    for (int i = t; i < ns; i += kSuperThreads) s_start[i] = recs[(size_t)i * kTileCountStride + 5];
+    if (t == 0) s_start[ns] = pairs;
+    __syncthreads();
+    const uint32_t chunks = (pairs + kSuperChunk - 1) / kSuperChunk;
+    for (uint32_t ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
+        uint32_t a = ch * kSuperChunk;
+        const uint32_t chunk_end = min(pairs, a + kSuperChunk);
+        // super-tile of the chunk's first entry: the last one whose list starts at or before it
+        int st = 0;
+        {
+            int lo = 0, hi = ns - 1;
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (s_start[mid] <= a) lo = mid; else hi = mid - 1; }
+            st = lo;
+        }
+        while (a < chunk_end) {                                       // one segment per super-tile the chunk spans
+            while (s_start[st + 1] <= a) ++st;                        // (skips empty lists)
+            const uint32_t b = min(chunk_end, s_start[st + 1]);
+            const uint32_t tx_lo = (uint32_t)(st % sgx) * kSuper, ty_lo = (uint32_t)(st / sgx) * kSuper;
+            const uint32_t tx_hi = min((uint32_t)grid_x, tx_lo + kSuper), ty_hi = min((uint32_t)grid_y, ty_lo + kSuper);
+            if (t < kSuper * kSuper) { s_cnt[t] = 0u; s_rank[t] = 0u; }
+            __syncthreads();
+            // this thread's entries: a + t, a + t + 256, ... (at most kSuperChunk / kSuperThreads of them)
+            for (uint32_t e = a + t; e < b; e += kSuperThreads) {
+                const int g = (int)__ldg(list + e);
+                uint2 rmin, rmax;
+                super_rect(means2D, radii, g, grid_x, grid_y, rmin, rmax);
+                const uint32_t x0 = max(rmin.x, tx_lo), x1 = min(rmax.x, tx_hi), y0 = max(rmin.y, ty_lo), y1 = min(rmax.y, ty_hi);
+                walk_rect(x0, x1, y0, y1, [&](uint32_t tx, uint32_t ty) { atomicAdd(&s_cnt[(ty - ty_lo) * kSuper + (tx - tx_lo)], 1u); });
+            }
+            __syncthreads();
+            if (t < kSuper * kSuper) {
+                const uint32_t c = s_cnt[t];
+                const uint32_t tx = tx_lo + (uint32_t)(t % kSuper), ty = ty_lo + (uint32_t)(t / kSuper);
+                if (c) s_cnt[t] = atomicAdd(recs + (size_t)(ty * grid_x + tx) * kTileCountStride + 2, c);   // base in the tile's segment
+            }
+            __syncthreads();
+            for (uint32_t e = a + t; e < b; e += kSuperThreads) {
+                const int g = (int)__ldg(list + e);
+                uint2 rmin, rmax;
+                super_rect(means2D, radii, g, grid_x, grid_y, rmin, rmax);
+                const uint32_t depth = __float_as_uint(__ldg(depths + g));
+                const uint32_t x0 = max(rmin.x, tx_lo), x1 = min(rmax.x, tx_hi), y0 = max(rmin.y, ty_lo), y1 = min(rmax.y, ty_hi);
+                const uint32_t w = rmax.x - rmin.x;
+                const uint32_t g_start = kRefOrder ? (g == 0 ? 0u : __ldg(offsets + g - 1)) : 0u;
+                walk_rect(x0, x1, y0, y1, [&](uint32_t tx, uint32_t ty) {
+                    const uint32_t local = (ty - ty_lo) * kSuper + (tx - tx_lo);
+                    const uint32_t tile = ty * (uint32_t)grid_x + tx;
+                    if (kRefOrder) {     // the reference's emission order: row-major over the Gaussian's rectangle
+                        const uint32_t slot = g_start + (ty - rmin.y) * w + (tx - rmin.x);
+                        keys_unsorted[slot] = ((uint64_t)tile << 32) | depth;
+                        vals_unsorted[slot] = (uint32_t)g;
+                    }
+                    words[s_cnt[local] + atomicAdd(&s_rank[local], 1u)] = ((uint64_t)depth << 32) | (uint32_t)g;
+                });
+            }
+            __syncthreads();
+            a = b;
+        }
+    }
+}
+
 constexpr int kTileSortThreads = 256;
 
 // Bitonic sort of n_pad = 256 * E words, E consecutive words per thread ("blocked"): compare distances
@@ -724,6 +891,23 @@ int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const Geo
     const int blocks = (P + kScatterThreads - 1) / kScatterThreads;
     const int tiles = grid_x * grid_y;
     const int hist_tiles = tiles <= 4096 ? tiles : 0;
+    // images beyond 1024^2 (more than 4096 tiles): two-level scatter over super-tiles (see super_emit_kernel)
+    const int ns = ((grid_x + kSuper - 1) / kSuper) * ((grid_y + kSuper - 1) / kSuper);
+    const char* force = getenv("GGD_SCATTER_SUPER");      // "1" / "0": force the choice (tests cover small images with it)
+    const bool super = ns <= kSuperMax && (force ? force[0] == '1' : tiles > 4096);
+    if (super) {
+        super_bin_kernel<true><<<blocks, kSuperThreads, 0, s>>>(P, grid_x, grid_y, g.means2D, radii, g.tile_counts, b.vals_tmp, g.counters);
+        GGD_LAUNCH_CHECK("super_bin_kernel<count>");
+        super_scan_kernel<<<1, kSuperMax, 0, s>>>(ns, g.tile_counts, g.counters);
+        GGD_LAUNCH_CHECK("super_scan_kernel");
+        super_bin_kernel<false><<<blocks, kSuperThreads, 0, s>>>(P, grid_x, grid_y, g.means2D, radii, g.tile_counts, b.vals_tmp, g.counters);
+        GGD_LAUNCH_CHECK("super_bin_kernel<write>");
+        auto emit = ref_order_arrays ? super_emit_kernel<true> : super_emit_kernel<false>;
+        emit<<<device_sm_count() * 8, kSuperThreads, 0, s>>>(grid_x, grid_y, g.means2D, g.depths, g.point_offsets, radii, b.keys_unsorted,
+                                                             b.vals_unsorted, b.keys_tmp, g.tile_counts, b.vals_tmp, g.counters);
+        GGD_LAUNCH_CHECK("super_emit_kernel");
+        return GGD_OK;
+    }
     auto kern = ref_order_arrays ? tile_scatter_kernel<true> : tile_scatter_kernel<false>;
     kern<<<blocks, kScatterThreads, sizeof(uint32_t) * 2 * (size_t)hist_tiles, s>>>(
         P, grid_x, grid_y, g.means2D, g.depths, g.point_offsets, radii, b.keys_unsorted, b.vals_unsorted, b.keys_tmp,

@@ -254,6 +254,28 @@ def test_bit_exact_elongated_rotated_splats(cuda, spread, size):
     assert_bit_exact(ours, ref, P)
 
 
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("P,W,H,trained", [(20_000, 256, 256, True), (50_000, 512, 512, False), (3000, 333, 100, True), (257, 40, 24, True)])
+def test_super_tile_scatter_bit_exact(cuda, monkeypatch, P, W, H, trained):
+    """Images beyond 1024^2 bin their instances in two levels (8x8-tile super-tiles first: super_bin / super_emit kernels);
+    GGD_SCATTER_SUPER=1 forces that path on small images, where the reference comparison is cheap (the 2048^2 test takes it
+    by itself).  Everything the reference returns must keep its bits, the emission-order arrays included; a second call and
+    a re-run of stage 2 on the same geometry state must give the same frame."""
+    monkeypatch.setenv("GGD_SCATTER_SUPER", "1")
+    s = synthetic.raster_scene(P, size=max(W, H), fov_deg=13.0, seed_offset=P % 53)
+    if not trained:
+        s = random_init_like(s, P)
+    s = to_dev(s, cuda)
+    s["W"], s["H"] = W, H
+    ref = RefCuda().forward(s, cuda)
+    for _ in range(2):
+        ours = run_ours(s, cuda)
+        assert_bit_exact(ours, ref, P)
+    monkeypatch.setenv("GGD_SCATTER_SUPER", "0")
+    other = run_ours(s, cuda)
+    assert torch.equal(other["out_color"], ours["out_color"]) and torch.equal(other["point_list"], ours["point_list"])
+
+
 def test_capacity_overflow_recovers(cuda):
     from gaussian_gan_decoder_b200 import rasterizer as rz
     s = to_dev(synthetic.raster_scene(20000, size=256, seed_offset=3), cuda)
@@ -431,9 +453,12 @@ def test_binning_clustered_depths(cuda, P, longest_at_least):
     assert_bit_exact(auto, radix, P)
 
 
-def test_stage2_rerun_on_same_geometry_state(cuda):
+@pytest.mark.parametrize("super_scatter", ["0", "1"])
+def test_stage2_rerun_on_same_geometry_state(cuda, monkeypatch, super_scatter):
     """ggd_raster_render may be called again on the state ggd_raster_preprocess left (the binding does that
-    after a capacity overflow; a caller may do it to change the background): same image, in both binning modes."""
+    after a capacity overflow; a caller may do it to change the background): same image, in both binning modes
+    (and with the two-level scatter of large images forced, whose super-tile counters live in the same state)."""
+    monkeypatch.setenv("GGD_SCATTER_SUPER", super_scatter)
     lib = _lib.load()
     P, size = 20_000, 160
     s = to_dev(synthetic.raster_scene(P, size=size, seed_offset=4), cuda)
