@@ -32,8 +32,15 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
              const float2* __restrict__ means2D, const float* __restrict__ features,
              const float4* __restrict__ conic_opacity, float* __restrict__ final_T,
              uint32_t* __restrict__ n_contrib, const float* __restrict__ bg,
-             float* __restrict__ out_color, uint32_t* __restrict__ work /*[2]: next tile, finished CTAs*/, uint32_t num_tiles)
+             float* __restrict__ out_color, uint32_t* __restrict__ work /*[2]: next tile, finished CTAs*/, uint32_t num_tiles,
+             uint32_t* __restrict__ recs /*tile records*/, const uint32_t* __restrict__ counters, const int round)
 {
+    // round 0: every tile, whole lists.  Lean pipelines sort long tile lists lazily (tile_sort_large_kernel): round 1 walks a
+    // long list only as far as it is sorted (word 7 of the tile's record) and marks the tile (word 8) when it gets there with
+    // live pixels; round 2 blends the marked tiles again, from the start, once their lists are sorted completely.  A tile that
+    // saturates inside the sorted part — almost all of them — has read exactly the instances it would read of the full order.
+    const bool lazy = round != 0 && __ldg(counters + 4) != 0u;      // (a frame that fell back to the radix sort has full lists)
+    if (round == 2 && !lazy) return;
     __shared__ uint32_t s_tile_id;
     __shared__ __align__(16) float4 s_rec[3 * kBatch];  // per instance: {x, y, conic.x, conic.y}, {conic.z, opacity, r, g}, {b, -, -, -}
     __shared__ uint32_t s_mask[kBatch];
@@ -54,6 +61,7 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
     __syncthreads();
     const uint32_t tile_id = s_tile_id;
     if (tile_id >= num_tiles) break;
+    if (round == 2 && recs[(size_t)tile_id * kTileCountStride + 8] == 0u) continue;
     const uint32_t tile_bx = tile_id % tiles_x, tile_by = tile_id / tiles_x;
     // warp w owns the 8x4 pixel block at (8*(w&1), 4*(w>>1)) of the tile
     const uint32_t px = tile_bx * kTileX + (warp & 1) * 8 + (lane & 7);
@@ -67,7 +75,9 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
     // no separate "done" branch; T keeps the value at termination for the output.
     float Tg = inside ? 1.0f : 0.0f;
 
-    const uint2 range = ranges[tile_id];
+    uint2 range = ranges[tile_id];
+    const uint32_t list_len = range.y - range.x;
+    if (lazy && round == 1 && list_len > kTileSortMax) range.y = range.x + min(list_len, recs[(size_t)tile_id * kTileCountStride + 7]);
     const int rounds = (int)((range.y - range.x + kBatch - 1) / kBatch);
     int to_do = (int)(range.y - range.x);
 
@@ -133,6 +143,10 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
         }
     }
 
+    if (lazy && round == 1) {      // not saturated at the end of the sorted part: the tile is done again in round 2
+        const int live = __syncthreads_count(Tg != 0.0f);
+        if (tr == 0) recs[(size_t)tile_id * kTileCountStride + 8] = (live != 0 && range.y - range.x < list_len) ? 1u : 0u;
+    }
     if (inside) {
         final_T[pix_id] = T;
         n_contrib[pix_id] = last_contributor;
@@ -150,7 +164,7 @@ blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ poin
 
 int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const GeomState& g,
                  const BinState& b, const ImgState& im, const float* features,
-                 const float* background, float* out_color)
+                 const float* background, float* out_color, int round)
 {
     const int sms = device_sm_count();
     const char* e = getenv("GGD_BLEND_CTAS");
@@ -159,7 +173,7 @@ int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const Geo
     const int grid = std::min(tiles, sms * per_sm);
     blend_kernel<<<grid, kTilePixels, 0, s>>>(im.ranges, b.vals, W, H, g.means2D, features,
                                               g.conic_opacity, im.accum_alpha, im.n_contrib, background,
-                                              out_color, g.counters + 8, (uint32_t)tiles);
+                                              out_color, g.counters + 8, (uint32_t)tiles, g.tile_counts, g.counters, round);
     GGD_LAUNCH_CHECK("blend_kernel");
     return GGD_OK;
 }

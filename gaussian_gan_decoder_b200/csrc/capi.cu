@@ -261,6 +261,9 @@ int ggd_raster_render(void* stream, int P, int W, int H, const float* background
     const int tiles = grid_x * grid_y;
     const bool per_tile = binning != 0 && bin_capacity > 0;
     const bool radix = !(per_tile && binning == 2);   // enqueue the radix kernels
+    // GGD_BINNING_LEAN on a large image: long tile lists are sorted only as far as the blend reads them (on 512^2 frames the
+    // second round costs more than the first saves: measured)
+    const bool lazy_sort = lean && per_tile && tiles > 4096;
     const int end_bit = 32 + tile_key_bits((uint32_t)tiles);
     const int num_passes = (end_bit + kRadixBits - 1) / kRadixBits;
 
@@ -279,14 +282,19 @@ int ggd_raster_render(void* stream, int P, int W, int H, const float* background
     }
     if (bin_capacity > 0) {
         { StageScope t(s, kStSort);
-          if (per_tile) if (int e = launch_tile_sort(s, g, b, im, tiles)) return e;
+          if (per_tile) if (int e = launch_tile_sort(s, g, b, im, tiles, lazy_sort ? 1 : 0)) return e;
           if (radix) if (int e = sort_pairs(s, b.keys_unsorted, b.keys, b.vals_unsorted, b.vals, g.counters + (per_tile ? 6 : 3),
                                             bin_capacity, 0, end_bit, b.keys_tmp, b.vals_tmp, sc, true)) return e; }
         { StageScope t(s, kStRanges); if (radix) if (int e = launch_tile_ranges(s, g, b, bin_capacity, im, tiles, skip)) return e; }
     }
     const float* features = colors_precomp ? colors_precomp : g.rgb;
     StageScope t(s, kStBlend);
-    return launch_blend(s, W, H, grid_x, grid_y, g, b, im, features, background, out_color);
+    if (!lazy_sort) return launch_blend(s, W, H, grid_x, grid_y, g, b, im, features, background, out_color);
+    // lean: long tile lists were sorted only in their nearest depth chunk.  Blend; sort the few lists that did not saturate
+    // inside it completely; blend those tiles again.  (All on the device: the second round's kernels skip unmarked tiles.)
+    if (int e = launch_blend(s, W, H, grid_x, grid_y, g, b, im, features, background, out_color, 1)) return e;
+    if (int e = launch_tile_sort(s, g, b, im, tiles, 2)) return e;
+    return launch_blend(s, W, H, grid_x, grid_y, g, b, im, features, background, out_color, 2);
 }
 
 int ggd_raster_forward(void* stream, int P, int D, int M, const float* background, int W, int H,

@@ -161,10 +161,10 @@ int launch_tile_scan(cudaStream_t s, const GeomState& g, const ImgState& im, int
 constexpr int kTileDiffMaxTiles = 16384;   // largest grid whose difference array tile_scan_kernel sums in shared memory (2048^2)
 int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const GeomState& g, const int* radii,
                         const BinState& b, const ImgState& im, uint64_t capacity, bool ref_order_arrays);
-int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, const ImgState& im, int tiles);
+int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, const ImgState& im, int tiles, int lazy = 0);
 int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const GeomState& g,
                  const BinState& b, const ImgState& im, const float* features,
-                 const float* background, float* out_color);
+                 const float* background, float* out_color, int round = 0);
 int launch_mark_visible(cudaStream_t s, int P, const float* means3D, const float* view,
                         const float* proj, uint8_t* present);
 

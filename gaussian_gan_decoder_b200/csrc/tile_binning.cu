@@ -649,6 +649,8 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ 
 // SM's shared memory, and an overfull bucket is sorted in place by the CTA with a comparison network.
 constexpr int kLargeThreads = 1024;
 constexpr uint32_t kLargeBuckets = 8192;
+constexpr uint32_t kLazyWords = 2048;      // target length of the nearest depth chunk in lazy mode (whole coarse bins: may be longer);
+                                           // 2048^2 / 2 M frame: 1024 -> 12.0 ms (too many second rounds), 2048 -> 7.1, 4096 -> 7.3, 8192 -> 7.9
 constexpr uint32_t kLargeInsertMax = 32;   // buckets up to this size are ordered by their owner thread
 // Lists up to this length are copied into the upper half of the CTA's shared memory first, so that the four passes
 // over the list (depth interval, coarse histogram, bucket histogram, distribution) read shared memory instead of
@@ -679,9 +681,14 @@ __device__ void cta_sort_range(uint64_t* __restrict__ s, uint32_t m)
 
 __global__ void __launch_bounds__(kLargeThreads, 1)
 tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ words, uint64_t* __restrict__ keys,
-                       uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters, const uint32_t* __restrict__ tile_list,
-                       uint32_t* __restrict__ status_flags)
+                       uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters, uint32_t* __restrict__ tile_list,
+                       uint32_t* __restrict__ status_flags, const int lazy, const uint32_t lazy_words)
 {
+    // lazy = 0: every long list, completely.  lazy = 1 (lean pipelines, first round): only the NEAREST depth chunk of every
+    // long list — the run of leading coarse bins holding up to kLazyWords words — whose length goes to word 7 of the tile's
+    // record: the blend leaves a tile when its pixels are saturated and on a dense frame reads 7-16 % of the lists (measured),
+    // so most of a complete sort is never looked at.  lazy = 2 (second round): the tiles the blend marked (word 8) because it
+    // reached the end of the sorted part with live pixels, completely; it then blends those tiles again.
     if (__ldg(counters + 4) == 0u) return;
     extern __shared__ __align__(16) uint8_t s_dyn[];
     uint64_t* s_out = reinterpret_cast<uint64_t*>(s_dyn);                                      // [kTileSortLargeMax]
@@ -694,11 +701,13 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t n_large = __ldg(counters + 7);
     for (uint32_t li = blockIdx.x; li < n_large; li += gridDim.x) {
-        const uint32_t tile = __ldg(tile_list + (size_t)li * kTileCountStride + 1);
+        const uint32_t tile = tile_list[(size_t)li * kTileCountStride + 1];
+        if (lazy == 2 && tile_list[(size_t)tile * kTileCountStride + 8] == 0u) continue;
         const uint2 range = ranges[tile];
         const uint32_t n = range.y - range.x;
         const uint64_t* gsrc = words + range.x;
-        const bool staged = n <= kLargeStagedMax;
+        bool staged = n <= kLargeStagedMax;
+        uint32_t n_walk = n;          // words the passes walk: the list, or (lazy round) its nearest chunk once gathered
         uint64_t* s_in = s_out + kLargeStagedMax;
         // One pass over the list: a thread's words are fetched kWalk at a time BEFORE any of them is used.  The passes
         // below update shared memory (atomics) per word; written as load-use-load-use a streamed list cost one L2 round
@@ -706,19 +715,19 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         constexpr int kWalk = 8;
         auto walk = [&](auto&& use) {
             if (staged) {      // the list sits in shared memory: nothing to batch
-                for (uint32_t i = t; i < n; i += kLargeThreads) use(s_in[i]);
+                for (uint32_t i = t; i < n_walk; i += kLargeThreads) use(s_in[i]);
                 return;
             }
-            for (uint32_t i0 = t; i0 < n; i0 += kWalk * kLargeThreads) {
+            for (uint32_t i0 = t; i0 < n_walk; i0 += kWalk * kLargeThreads) {
                 uint64_t w[kWalk];
 #pragma unroll
                 for (int k = 0; k < kWalk; ++k) {
                     const uint32_t i = i0 + (uint32_t)k * kLargeThreads;
-                    w[k] = i < n ? __ldg(gsrc + i) : 0ull;
+                    w[k] = i < n_walk ? __ldg(gsrc + i) : 0ull;
                 }
 #pragma unroll
                 for (int k = 0; k < kWalk; ++k)
-                    if (i0 + (uint32_t)k * kLargeThreads < n) use(w[k]);
+                    if (i0 + (uint32_t)k * kLargeThreads < n_walk) use(w[k]);
             }
         };
         // depth interval of the list
@@ -759,15 +768,31 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         __syncthreads();
         coarse_scan(s_c, s_cstart);
         __syncthreads();
+        if (lazy == 1 && !staged) {
+            // Lazy round on a list that streams from L2: gather the nearest chunk into shared memory once and sort it there —
+            // the two passes of the chunk's bucket sort then walk its few thousand words instead of the whole list.
+            uint32_t c1 = 1;
+            while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] <= lazy_words) ++c1;
+            const uint32_t m = s_cstart[c1];
+            if (m <= kLargeStagedMax) {
+                if (t == 0) s_nbig = 0;
+                __syncthreads();
+                walk([&](uint64_t w) { if (coarse_of(w) < c1) s_in[atomicAdd(&s_nbig, 1u)] = w; });
+                __syncthreads();
+                n_walk = m;
+                staged = true;
+            }
+        }
         // A list longer than the shared-memory buffer is sorted in depth chunks: runs of coarse bins [c0, c1) holding at
         // most kTileSortLargeMax words each, one after the other (a coarse bin is monotone in depth and equal depths share
         // a bin, so the chunks' sorted runs concatenate to the sorted list).  Every chunk re-reads the list from L2.
         uint32_t c0 = 0;
         while (c0 < (uint32_t)kCoarse) {
             uint32_t c1 = kCoarse;                      // a list that fits the buffer is one chunk: no walk over the bins
-            if (n > kTileSortLargeMax) {
+            if (n > kTileSortLargeMax || lazy == 1) {
+                const uint32_t room = lazy == 1 ? lazy_words : kTileSortLargeMax;
                 c1 = c0 + 1;
-                while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] - s_cstart[c0] <= kTileSortLargeMax) ++c1;
+                while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] - s_cstart[c0] <= room) ++c1;
             }
             const uint32_t first = s_cstart[c0], m_chunk = s_cstart[c1] - first;
             const bool whole = (c0 == 0 && c1 == (uint32_t)kCoarse);
@@ -866,7 +891,9 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
             }
             __syncthreads();
             c0 = c1;
+            if (lazy == 1) break;                       // the nearest chunk only
         }
+        if (t == 0 && lazy != 0) tile_list[(size_t)tile * kTileCountStride + 7] = lazy == 1 ? s_cstart[c0] : n;   // sorted so far
         __syncthreads();
     }
 }
@@ -916,8 +943,16 @@ int launch_tile_scatter(cudaStream_t s, int P, int grid_x, int grid_y, const Geo
     return GGD_OK;
 }
 
-int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, const ImgState& im, int tiles)
+int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, const ImgState& im, int tiles, int lazy)
 {
+    if (lazy == 2) {      // second round: the marked long lists only
+        int sms2 = device_sm_count();
+        constexpr int smem2 = (int)(sizeof(uint64_t) * kTileSortLargeMax + sizeof(uint32_t) * kLargeBuckets);
+        tile_sort_large_kernel<<<std::min(tiles, sms2), kLargeThreads, smem2, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters,
+                                                                                  g.tile_counts, g.counters + 1, 2, kLazyWords);
+        GGD_LAUNCH_CHECK("tile_sort_large_kernel<round 2>");
+        return GGD_OK;
+    }
     constexpr int smem = (int)((sizeof(uint64_t) + sizeof(uint32_t)) * kTileSortMax);
     GGD_CUDA_CHECK(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     tile_sort_kernel<<<tiles, kTileSortThreads, smem, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters);
@@ -928,7 +963,7 @@ int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, cons
     { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
     // (the flag word is counters[1]; passed as its own pointer because `counters` is read through the read-only path)
     tile_sort_large_kernel<<<std::min(tiles, sms), kLargeThreads, smem_large, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters,
-                                                                                  g.tile_counts, g.counters + 1);
+                                                                                  g.tile_counts, g.counters + 1, lazy, kLazyWords);
     GGD_LAUNCH_CHECK("tile_sort_large_kernel");
     return GGD_OK;
 }

@@ -157,7 +157,10 @@ GGD_API int ggd_raster_status(void* stream, const void* geom_ws, int P, uint32_t
 #define GGD_BINNING_TILES 2
 /* Or-ed into a mode: a frame binned per tile does not write the reference-order arrays "point_list_keys_unsorted" /
  * "point_list_unsorted" (duplicateWithKeys' output, 12 bytes per instance, read by nothing but ggd_raster_field
- * users); sorted keys, point list, ranges and everything downstream are unchanged.  For frame loops. */
+ * users).  On images of more than 4096 tiles it also sorts a long tile list only as far as the blend reads it (the
+ * nearest depth chunk; a tile whose pixels are not saturated by then is sorted completely and blended again): image,
+ * final T, contributor counts and the list prefix the backward replays are unchanged, "point_list" /
+ * "point_list_keys" beyond that prefix are not in order.  For frame loops. */
 #define GGD_BINNING_LEAN 4
 /* Sets the process DEFAULT used by calls that pass GGD_BINNING_DEFAULT; pass -1 to query.  Returns the
  * previous default. */

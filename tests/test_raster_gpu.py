@@ -276,6 +276,54 @@ def test_super_tile_scatter_bit_exact(cuda, monkeypatch, P, W, H, trained):
     assert torch.equal(other["out_color"], ours["out_color"]) and torch.equal(other["point_list"], ours["point_list"])
 
 
+@pytest.mark.parametrize("backward", [False, True])
+def test_lean_large_image_sorts_lazily_same_frame(cuda, backward):
+    """GGD_BINNING_LEAN on an image beyond 1024^2: long tile lists are sorted only in their nearest depth chunk, the blend
+    marks the tiles that did not saturate inside it, those are sorted completely and blended again.  Image, final T and
+    contributor counts must be the bits of the complete path, and the backward (which replays the lists from the last
+    contributor) must see the same gradients."""
+    from gaussian_gan_decoder_b200 import rasterizer as rz
+    _C = rz._C
+    P, S = 1_500_000, 1040                                 # 65 x 65 tiles, ~13k instances per tile
+    s = to_dev(synthetic.raster_scene(P, size=S, fov_deg=12.0, seed_offset=77), cuda)
+    e = torch.empty(0, device=cuda)
+
+    def run(keep):
+        old = rz.keep_reference_order_arrays
+        rz.keep_reference_order_arrays = keep
+        try:
+            out = rz._C.rasterize_gaussians(s["bg"], s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e, s["viewmatrix"],
+                                            s["projmatrix"], s["tanfovx"], s["tanfovy"], S, S, s["shs"], 0, s["campos"], False, False)
+        finally:
+            rz.keep_reference_order_arrays = old
+        return out
+
+    full, lean = run(True), run(False)
+    R, cap = full[0], getattr(full[4], "ggd_capacity", 0)
+    info = (C.c_uint32 * 2)()
+    _lib.check(_lib.load().ggd_raster_binning_info(None, _lib.ptr(lean[3]), P, info))
+    assert info[0] == 1 and info[1] > 3 * 4096, tuple(info)           # binned per tile, lists long enough for the lazy path
+    assert lean[0] == R and torch.equal(lean[1], full[1]) and torch.equal(lean[2], full[2])
+    for name, dt in (("accum_alpha", torch.float32), ("n_contrib", torch.int32), ("ranges", torch.int32)):
+        a = rz.field(full[5], 2, name, P, S, S, cap, dt)
+        b = rz.field(lean[5], 2, name, P, S, S, cap, dt)
+        assert torch.equal(a, b), name
+    if backward:
+        dL = torch.randn(3, S, S, generator=synthetic.gen(5)).to(cuda)
+        grads = []
+        for o in (full, full, lean):     # the backward sums with float atomics: its own run-to-run spread is the yardstick
+            grads.append(_C.rasterize_gaussians_backward(s["bg"], s["means3D"], o[2], e, s["scales"], s["rotations"], 1.0, e, s["viewmatrix"],
+                                                         s["projmatrix"], s["tanfovx"], s["tanfovy"], dL, s["shs"], 0, s["campos"], o[3], R,
+                                                         o[4], o[5], False))
+        torch.cuda.synchronize()
+        for ga, gb, gc in zip(*grads):
+            if ga.numel():
+                scale = float(ga.abs().max()) + 1e-30
+                spread = float((ga - gb).abs().max())
+                assert float((gc - ga).abs().max()) <= max(4.0 * spread, 1e-5 * scale), (float((gc - ga).abs().max()), spread, scale)
+                assert spread <= 1e-3 * scale
+
+
 def test_capacity_overflow_recovers(cuda):
     from gaussian_gan_decoder_b200 import rasterizer as rz
     s = to_dev(synthetic.raster_scene(20000, size=256, seed_offset=3), cuda)
