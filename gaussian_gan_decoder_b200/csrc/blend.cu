@@ -27,14 +27,18 @@ namespace {
 constexpr int kBatch = 2 * kTilePixels;  // instances staged per round (two per thread): half as many CTA barriers as with 256,
                                          // at which the eight warps of a tile wait for the slowest one's hit list
 
-__global__ void __launch_bounds__(kTilePixels, 6)      // six CTAs per SM: at most 40 registers
+template <int kRound>      // 0: plain; 1 / 2: the two rounds of a lazily sorted frame (see below) — a template argument so that
+                           // the plain kernel keeps its register allocation
+__global__ void __launch_bounds__(kTilePixels)         // 40 registers: six CTAs per SM (asking ptxas for that with a
+                                                       // min-blocks bound cost the hit loop its uniform-register addressing)
 blend_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
              const float2* __restrict__ means2D, const float* __restrict__ features,
              const float4* __restrict__ conic_opacity, float* __restrict__ final_T,
              uint32_t* __restrict__ n_contrib, const float* __restrict__ bg,
              float* __restrict__ out_color, uint32_t* __restrict__ work /*[2]: next tile, finished CTAs*/, uint32_t num_tiles,
-             uint32_t* __restrict__ recs /*tile records*/, const uint32_t* __restrict__ counters, const int round)
+             uint32_t* __restrict__ recs /*tile records*/, const uint32_t* __restrict__ counters)
 {
+    constexpr int round = kRound;
     // round 0: every tile, whole lists.  Lean pipelines sort long tile lists lazily (tile_sort_large_kernel): round 1 walks a
     // long list only as far as it is sorted (word 7 of the tile's record) and marks the tile (word 8) when it gets there with
     // live pixels; round 2 blends the marked tiles again, from the start, once their lists are sorted completely.  A tile that
@@ -171,9 +175,9 @@ int launch_blend(cudaStream_t s, int W, int H, int grid_x, int grid_y, const Geo
     const int per_sm = e ? atoi(e) : 6;
     const int tiles = grid_x * grid_y;
     const int grid = std::min(tiles, sms * per_sm);
-    blend_kernel<<<grid, kTilePixels, 0, s>>>(im.ranges, b.vals, W, H, g.means2D, features,
-                                              g.conic_opacity, im.accum_alpha, im.n_contrib, background,
-                                              out_color, g.counters + 8, (uint32_t)tiles, g.tile_counts, g.counters, round);
+    auto kern = round == 0 ? blend_kernel<0> : round == 1 ? blend_kernel<1> : blend_kernel<2>;
+    kern<<<grid, kTilePixels, 0, s>>>(im.ranges, b.vals, W, H, g.means2D, features, g.conic_opacity, im.accum_alpha, im.n_contrib,
+                                      background, out_color, g.counters + 8, (uint32_t)tiles, g.tile_counts, g.counters);
     GGD_LAUNCH_CHECK("blend_kernel");
     return GGD_OK;
 }

@@ -4,6 +4,36 @@
 
 namespace ggd {
 
+// Second test of warp_block_mask (see there), for splats larger than a block.  Not inlined: inside the blend kernel its
+// arithmetic raised the register allocation of the whole kernel by four and cost the per-hit loop its uniform-register
+// addressing (3 more instructions per hit, +4.5 % on the frame of small splats that never gets here).
+static __device__ __noinline__ uint32_t refine_block_mask(uint32_t box, float cx, float cy, float a, float b, float c, float s)
+{
+    const float nb_over_c = -b / c, nb_over_a = -b / a, s_far = s * 1.01f;
+    uint32_t m = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        const float bx0 = (float)((w & 1) * 8), by0 = (float)((w >> 1) * 4);
+        if (!((box >> w) & 1u)) continue;
+        const float dx0 = cx - bx0 - 7.f, dx1 = cx - bx0, dy0 = cy - by0 - 3.f, dy1 = cy - by0;   // d = centre - pixel
+        const float ex = fminf(fmaxf(0.f, dx0), dx1), ey = fminf(fmaxf(0.f, dy0), dy1);
+        float qmin = 0.f;
+        if (ex != 0.f || ey != 0.f) {
+            qmin = 3.0e38f;
+            if (ex != 0.f) {
+                const float dy = fminf(fmaxf(nb_over_c * ex, dy0), dy1);
+                qmin = fminf(qmin, a * ex * ex + dy * (2.f * b * ex + c * dy));
+            }
+            if (ey != 0.f) {
+                const float dx = fminf(fmaxf(nb_over_a * ey, dx0), dx1);
+                qmin = fminf(qmin, c * ey * ey + dx * (2.f * b * ey + a * dx));
+            }
+        }
+        if (!(qmin > s_far)) m |= 1u << w;     // NaN keeps the block
+    }
+    return m;
+}
+
 // Conservative footprint test.  An instance can only change a pixel if
 // alpha = min(0.99, o * exp(power)) >= 1/255, i.e. d^T Q d <= 2 ln(255 o) with Q the conic.
 // The staging thread turns that ellipse into a pixel-space box, inflated by 1 % (the fp32
@@ -37,30 +67,7 @@ __device__ __forceinline__ uint32_t warp_block_mask(float x, float y, float a, f
         if (lx1 >= bx0 && lx0 <= bx0 + 7.f && ly1 >= by0 && ly0 <= by0 + 3.f) box |= 1u << w;
     }
     if (!(rx + ry > 6.0f)) return box;
-    const float cx = x - tile_x0, cy = y - tile_y0;
-    const float nb_over_c = -b / c, nb_over_a = -b / a, s_far = s * 1.01f;
-    uint32_t m = 0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) {
-        const float bx0 = (float)((w & 1) * 8), by0 = (float)((w >> 1) * 4);
-        if (!((box >> w) & 1u)) continue;
-        const float dx0 = cx - bx0 - 7.f, dx1 = cx - bx0, dy0 = cy - by0 - 3.f, dy1 = cy - by0;   // d = centre - pixel
-        const float ex = fminf(fmaxf(0.f, dx0), dx1), ey = fminf(fmaxf(0.f, dy0), dy1);
-        float qmin = 0.f;
-        if (ex != 0.f || ey != 0.f) {
-            qmin = 3.0e38f;
-            if (ex != 0.f) {
-                const float dy = fminf(fmaxf(nb_over_c * ex, dy0), dy1);
-                qmin = fminf(qmin, a * ex * ex + dy * (2.f * b * ex + c * dy));
-            }
-            if (ey != 0.f) {
-                const float dx = fminf(fmaxf(nb_over_a * ey, dx0), dx1);
-                qmin = fminf(qmin, c * ey * ey + dx * (2.f * b * ey + a * dx));
-            }
-        }
-        if (!(qmin > s_far)) m |= 1u << w;     // NaN keeps the block
-    }
-    return m;
+    return refine_block_mask(box, x - tile_x0, y - tile_y0, a, b, c, s);
 }
 
 }  // namespace ggd
