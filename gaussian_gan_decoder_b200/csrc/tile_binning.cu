@@ -527,7 +527,8 @@ __device__ __forceinline__ void coarse_scan(const uint32_t* __restrict__ s_c, ui
     }
 }
 
-template <int E>
+// kFromShared: the n words wait in s_out[0..n) (gathered there by the caller) instead of words[begin..]
+template <int E, bool kFromShared = false>
 __device__ __forceinline__ void dist_sort_tile(uint64_t* __restrict__ s_out, uint32_t* __restrict__ s_hist,
                                                const uint64_t* __restrict__ words, uint32_t begin, uint32_t n, uint32_t tile,
                                                uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
@@ -543,7 +544,7 @@ __device__ __forceinline__ void dist_sort_tile(uint64_t* __restrict__ s_out, uin
 #pragma unroll
     for (int r = 0; r < E; ++r) {
         const uint32_t i = t + r * kTileSortThreads;
-        w[r] = i < n ? __ldg(words + begin + i) : ~0ull;
+        w[r] = i < n ? (kFromShared ? s_out[i] : __ldg(words + begin + i)) : ~0ull;
         if (i < n) { dmin = min(dmin, (uint32_t)(w[r] >> 32)); dmax = max(dmax, (uint32_t)(w[r] >> 32)); }
         s_hist[i] = 0;
     }
@@ -644,13 +645,89 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ 
     else dist_sort_tile<16>(s, h, words, range.x, n, tile, keys, vals);
 }
 
+// First round of a lazily sorted frame (lean pipelines on large images, see tile_sort_large_kernel's `lazy`): for every long
+// list, the nearest depth chunk — the leading coarse bins holding about kLazyWords words — is gathered into shared memory
+// and sorted there with the small lists' routine; its length goes to word 7 of the tile's record.  Three passes over the
+// list (depth interval, coarse histogram, gather) that wait for L2 / DRAM most of the time: 256-thread CTAs, four per SM,
+// so that several lists are in flight on an SM (the 1024-thread kernel did this round at one list per SM: 2.5 ms on the
+// 2048^2 / 2 M frame).  A list whose first coarse bin alone holds more than kLazyWords words gets length 0: the blend then marks
+// the tile and the second round sorts it completely.
+constexpr uint32_t kLazyWords = 2048;      // 2048^2 / 2 M frame: 1024 -> 12.0 ms (too many second rounds), 2048 -> 7.1, 4096 -> 7.3, 8192 -> 7.9
+static_assert(kLazyWords == 8 * kTileSortThreads, "tile_sort_lazy_kernel sorts its chunk with dist_sort_tile<8>");
+__global__ void __launch_bounds__(kTileSortThreads, 4)
+tile_sort_lazy_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ words, uint64_t* __restrict__ keys,
+                      uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters, uint32_t* __restrict__ recs)
+{
+    if (__ldg(counters + 4) == 0u) return;
+    extern __shared__ __align__(16) uint8_t s_dyn[];
+    uint64_t* s = reinterpret_cast<uint64_t*>(s_dyn);                              // [kTileSortMax]
+    uint32_t* h = reinterpret_cast<uint32_t*>(s_dyn + sizeof(uint64_t) * kTileSortMax);   // [kTileSortMax]
+    __shared__ uint32_t s_red[2][kTileSortThreads / 32];
+    __shared__ uint32_t s_c[kCoarse], s_cstart[kCoarse + 1];
+    __shared__ uint32_t s_n;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t n_large = __ldg(counters + 7);
+    constexpr int kWalk = 8;
+    for (uint32_t li = blockIdx.x; li < n_large; li += gridDim.x) {
+        const uint32_t tile = recs[(size_t)li * kTileCountStride + 1];
+        const uint2 range = ranges[tile];
+        const uint32_t n = range.y - range.x;
+        const uint64_t* src = words + range.x;
+        auto walk = [&](auto&& use) {
+            for (uint32_t i0 = t; i0 < n; i0 += kWalk * kTileSortThreads) {
+                uint64_t w[kWalk];
+#pragma unroll
+                for (int k = 0; k < kWalk; ++k) {
+                    const uint32_t i = i0 + (uint32_t)k * kTileSortThreads;
+                    w[k] = i < n ? __ldg(src + i) : 0ull;
+                }
+#pragma unroll
+                for (int k = 0; k < kWalk; ++k)
+                    if (i0 + (uint32_t)k * kTileSortThreads < n) use(w[k]);
+            }
+        };
+        uint32_t dmin = 0xffffffffu, dmax = 0u;
+        walk([&](uint64_t w) { const uint32_t d = (uint32_t)(w >> 32); dmin = min(dmin, d); dmax = max(dmax, d); });
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            dmin = min(dmin, __shfl_xor_sync(0xffffffffu, dmin, o));
+            dmax = max(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+        }
+        if (lane == 0) { s_red[0][warp] = dmin; s_red[1][warp] = dmax; }
+        if (t < kCoarse) s_c[t] = 0;
+        if (t == 0) s_n = 0;
+        __syncthreads();
+        for (int k = 0; k < kTileSortThreads / 32; ++k) { dmin = min(dmin, s_red[0][k]); dmax = max(dmax, s_red[1][k]); }
+        const float scale_c = (float)kCoarse / ((float)(dmax - dmin) + 1.0f);
+        auto coarse_of = [&](uint64_t w) { return min((uint32_t)(kCoarse - 1), (uint32_t)((float)((uint32_t)(w >> 32) - dmin) * scale_c)); };
+        walk([&](uint64_t w) { atomicAdd(&s_c[coarse_of(w)], 1u); });
+        __syncthreads();
+        coarse_scan(s_c, s_cstart);
+        __syncthreads();
+        uint32_t c1 = 1;
+        while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] <= kLazyWords) ++c1;
+        const uint32_t m = s_cstart[c1];
+        if (m > kLazyWords) {                         // (uniform) the first bin alone is too long for this kernel
+            if (t == 0) recs[(size_t)tile * kTileCountStride + 7] = 0u;
+            __syncthreads();
+            continue;
+        }
+        walk([&](uint64_t w) { if (coarse_of(w) < c1) s[atomicAdd(&s_n, 1u)] = w; });
+        __syncthreads();
+        if (m <= 256) dist_sort_tile<1, true>(s, h, nullptr, range.x, m, tile, keys, vals);
+        else if (m <= 512) dist_sort_tile<2, true>(s, h, nullptr, range.x, m, tile, keys, vals);
+        else if (m <= 1024) dist_sort_tile<4, true>(s, h, nullptr, range.x, m, tile, keys, vals);
+        else dist_sort_tile<8, true>(s, h, nullptr, range.x, m, tile, keys, vals);       // m <= kLazyWords = 2048
+        if (t == 0) recs[(size_t)tile * kTileCountStride + 7] = m;
+        __syncthreads();
+    }
+}
+
 // Long tile lists (kTileSortMax < n <= kTileSortLargeMax): same distribution sort, but the list stays in
 // global memory (L2) for two streaming passes instead of registers, one CTA of 1024 threads owns a whole
 // SM's shared memory, and an overfull bucket is sorted in place by the CTA with a comparison network.
 constexpr int kLargeThreads = 1024;
 constexpr uint32_t kLargeBuckets = 8192;
-constexpr uint32_t kLazyWords = 2048;      // target length of the nearest depth chunk in lazy mode (whole coarse bins: may be longer);
-                                           // 2048^2 / 2 M frame: 1024 -> 12.0 ms (too many second rounds), 2048 -> 7.1, 4096 -> 7.3, 8192 -> 7.9
 constexpr uint32_t kLargeInsertMax = 32;   // buckets up to this size are ordered by their owner thread
 // Lists up to this length are copied into the upper half of the CTA's shared memory first, so that the four passes
 // over the list (depth interval, coarse histogram, bucket histogram, distribution) read shared memory instead of
@@ -682,13 +759,11 @@ __device__ void cta_sort_range(uint64_t* __restrict__ s, uint32_t m)
 __global__ void __launch_bounds__(kLargeThreads, 1)
 tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ words, uint64_t* __restrict__ keys,
                        uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters, uint32_t* __restrict__ tile_list,
-                       uint32_t* __restrict__ status_flags, const int lazy, const uint32_t lazy_words)
+                       uint32_t* __restrict__ status_flags, const int lazy)
 {
-    // lazy = 0: every long list, completely.  lazy = 1 (lean pipelines, first round): only the NEAREST depth chunk of every
-    // long list — the run of leading coarse bins holding up to kLazyWords words — whose length goes to word 7 of the tile's
-    // record: the blend leaves a tile when its pixels are saturated and on a dense frame reads 7-16 % of the lists (measured),
-    // so most of a complete sort is never looked at.  lazy = 2 (second round): the tiles the blend marked (word 8) because it
-    // reached the end of the sorted part with live pixels, completely; it then blends those tiles again.
+    // lazy = 0: every long list.  lazy = 2: second round of a lazily sorted frame (lean pipelines on large images; the first
+    // round is tile_sort_lazy_kernel): only the tiles the blend marked (word 8 of the tile's record) because it reached the
+    // end of the sorted chunk with live pixels; they are then blended again.
     if (__ldg(counters + 4) == 0u) return;
     extern __shared__ __align__(16) uint8_t s_dyn[];
     uint64_t* s_out = reinterpret_cast<uint64_t*>(s_dyn);                                      // [kTileSortLargeMax]
@@ -768,31 +843,15 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
         __syncthreads();
         coarse_scan(s_c, s_cstart);
         __syncthreads();
-        if (lazy == 1 && !staged) {
-            // Lazy round on a list that streams from L2: gather the nearest chunk into shared memory once and sort it there —
-            // the two passes of the chunk's bucket sort then walk its few thousand words instead of the whole list.
-            uint32_t c1 = 1;
-            while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] <= lazy_words) ++c1;
-            const uint32_t m = s_cstart[c1];
-            if (m <= kLargeStagedMax) {
-                if (t == 0) s_nbig = 0;
-                __syncthreads();
-                walk([&](uint64_t w) { if (coarse_of(w) < c1) s_in[atomicAdd(&s_nbig, 1u)] = w; });
-                __syncthreads();
-                n_walk = m;
-                staged = true;
-            }
-        }
         // A list longer than the shared-memory buffer is sorted in depth chunks: runs of coarse bins [c0, c1) holding at
         // most kTileSortLargeMax words each, one after the other (a coarse bin is monotone in depth and equal depths share
         // a bin, so the chunks' sorted runs concatenate to the sorted list).  Every chunk re-reads the list from L2.
         uint32_t c0 = 0;
         while (c0 < (uint32_t)kCoarse) {
             uint32_t c1 = kCoarse;                      // a list that fits the buffer is one chunk: no walk over the bins
-            if (n > kTileSortLargeMax || lazy == 1) {
-                const uint32_t room = lazy == 1 ? lazy_words : kTileSortLargeMax;
+            if (n > kTileSortLargeMax) {
                 c1 = c0 + 1;
-                while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] - s_cstart[c0] <= room) ++c1;
+                while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] - s_cstart[c0] <= kTileSortLargeMax) ++c1;
             }
             const uint32_t first = s_cstart[c0], m_chunk = s_cstart[c1] - first;
             const bool whole = (c0 == 0 && c1 == (uint32_t)kCoarse);
@@ -891,9 +950,8 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint64_t* __restr
             }
             __syncthreads();
             c0 = c1;
-            if (lazy == 1) break;                       // the nearest chunk only
         }
-        if (t == 0 && lazy != 0) tile_list[(size_t)tile * kTileCountStride + 7] = lazy == 1 ? s_cstart[c0] : n;   // sorted so far
+        if (t == 0 && lazy != 0) tile_list[(size_t)tile * kTileCountStride + 7] = n;   // sorted completely now
         __syncthreads();
     }
 }
@@ -949,7 +1007,7 @@ int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, cons
         int sms2 = device_sm_count();
         constexpr int smem2 = (int)(sizeof(uint64_t) * kTileSortLargeMax + sizeof(uint32_t) * kLargeBuckets);
         tile_sort_large_kernel<<<std::min(tiles, sms2), kLargeThreads, smem2, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters,
-                                                                                  g.tile_counts, g.counters + 1, 2, kLazyWords);
+                                                                                  g.tile_counts, g.counters + 1, 2);
         GGD_LAUNCH_CHECK("tile_sort_large_kernel<round 2>");
         return GGD_OK;
     }
@@ -962,8 +1020,15 @@ int launch_tile_sort(cudaStream_t s, const GeomState& g, const BinState& b, cons
     int sms = 148;
     { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
     // (the flag word is counters[1]; passed as its own pointer because `counters` is read through the read-only path)
+    if (lazy == 1) {      // first round of a lazily sorted frame: the nearest depth chunk of every long list
+        GGD_CUDA_CHECK(cudaFuncSetAttribute(tile_sort_lazy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        tile_sort_lazy_kernel<<<std::min(tiles, 4 * sms), kTileSortThreads, smem, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters,
+                                                                                      g.tile_counts);
+        GGD_LAUNCH_CHECK("tile_sort_lazy_kernel");
+        return GGD_OK;
+    }
     tile_sort_large_kernel<<<std::min(tiles, sms), kLargeThreads, smem_large, s>>>(im.ranges, b.keys_tmp, b.keys, b.vals, g.counters,
-                                                                                  g.tile_counts, g.counters + 1, lazy, kLazyWords);
+                                                                                  g.tile_counts, g.counters + 1, 0);
     GGD_LAUNCH_CHECK("tile_sort_large_kernel");
     return GGD_OK;
 }
