@@ -12,18 +12,24 @@
 // launch with a chained look-back; at the frame sizes of the headline workload (R ~ 10^6 instances,
 // ~800 per tile) that is latency, not bandwidth.  Here an instance is written once into its tile's
 // segment and sorted where it lands:
-//   preprocess        counts instances per tile (atomics, fused into the projection kernel)
-//   tile_scan_kernel  exclusive scan of the counts -> ranges[tile] = [start, end) ((0,0) for an empty
-//                     tile, as the reference leaves it); sets up each tile's write cursor; decides
-//                     whether the frame qualifies (longest list <= kTileSortHugeMax,
-//                     R <= capacity)
+//   preprocess        counts instances per tile (atomics, fused into the projection kernel; rectangles of 32
+//                     tiles or more as +1 / -1 at their corners of a 2-D difference array)
+//   tile_scan_kernel  sums the difference array (2-D prefix sum), exclusive scan of the counts ->
+//                     ranges[tile] = [start, end) ((0,0) for an empty tile, as the reference leaves it); sets up
+//                     each tile's write cursor; decides whether the frame qualifies (longest list <=
+//                     kTileSortHugeMax, R <= capacity)
 //   tile_scatter      slot-centric like duplicate_kernel; claims a slot in the tile's segment with an
-//                     atomic on the tile's cursor
+//                     atomic on the tile's cursor (CTAs of large splats: one atomic per tile, ranks in shared memory)
+//   super_bin / super_scan / super_emit   the scatter of images with more than 4096 tiles, in two levels: Gaussians
+//                     are binned by 8x8-tile super-tile, a CTA then claims a list chunk's places per tile in shared memory
 //   tile_sort_kernel  one CTA per tile: distribution sort of the 64-bit words in shared memory (bitonic
 //                     network for lists with heavily clustered depths)
 //   tile_sort_large_kernel  the same for lists of 4097..98304 instances: persistent CTAs of 1024 threads,
 //                     one per SM, walk the list of long tiles the scan wrote; lists beyond 24576 words are
 //                     sorted in depth chunks
+//   tile_sort_lazy_kernel   lean pipelines on large images: only the nearest depth chunk of every long list (the blend
+//                     reads 7-16 % of a dense frame's sorted instances); the tiles whose pixels outlive it are marked
+//                     by the blend, sorted completely (tile_sort_large_kernel, lazy = 2) and blended again
 // Frames that do not qualify (a tile list longer than kTileSortHugeMax) take the radix path of binning.cu;
 // the decision is made on the device (counters[4]) and both sets of kernels are always enqueued, the
 // ones that do not apply return at once, so no host round trip is needed.
