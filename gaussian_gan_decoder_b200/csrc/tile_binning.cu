@@ -209,28 +209,43 @@ tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ me
         uint32_t* s_rank = s_scatter + hist_tiles;
         for (int i = t; i < hist_tiles; i += kScatterThreads) { s_base[i] = 0u; s_rank[i] = 0u; }
         __syncthreads();
-        for (uint32_t k = t; k < n_slots; k += kScatterThreads) {
-            int g; uint32_t tile;
-            locate(block_start + k, g, tile);
-            atomicAdd(&s_base[tile], 1u);
-        }
+        // Both passes give every thread a run of CONSECUTIVE slots: one search for the run's first slot, then the walk
+        // steps from tile to tile of a rectangle and from Gaussian to Gaussian.  (With slots t, t + 256, ... every slot
+        // pays locate()'s 8-step binary search and integer division — twice here: 212 instructions per instance on a
+        // trained-like frame, the kernel was instruction-bound.)
+        const uint32_t per = (n_slots + kScatterThreads - 1) / kScatterThreads;
+        const uint32_t k_begin = min(n_slots, (uint32_t)t * per), k_end = min(n_slots, k_begin + per);
+        auto walk = [&](auto&& emit) {
+            if (k_begin >= k_end) return;
+            uint32_t s = block_start + k_begin;
+            int g; uint32_t tile_unused;
+            locate(s, g, tile_unused);
+            uint32_t g_start = (g == 0) ? block_start : s_end[g - 1];
+            uint32_t g_end = s_end[g], w = s_w[g], rc = s_rect[g];
+            uint32_t row = (s - g_start) / w, col = (s - g_start) - row * w;
+            for (; s < block_start + k_end; ++s) {
+                while (s >= g_end) {                   // next Gaussian with instances (s < block_end = s_end[last])
+                    ++g; g_end = s_end[g]; w = s_w[g]; rc = s_rect[g]; row = 0; col = 0;
+                }
+                emit(g, s, ((rc >> 16) + row) * (uint32_t)grid_x + (rc & 0xffffu) + col);
+                if (++col == w) { col = 0; ++row; }
+            }
+        };
+        walk([&](int, uint32_t, uint32_t tile) { atomicAdd(&s_base[tile], 1u); });
         __syncthreads();
         for (int i = t; i < hist_tiles; i += kScatterThreads) {
             const uint32_t c = s_base[i];
             if (c) s_base[i] = atomicAdd(cursors + (size_t)i * kTileCountStride + 2, c);   // the CTA's base in the tile's segment
         }
         __syncthreads();
-        for (uint32_t k = t; k < n_slots; k += kScatterThreads) {
-            const uint32_t s = block_start + k;
-            int g; uint32_t tile;
-            locate(s, g, tile);
+        walk([&](int g, uint32_t s, uint32_t tile) {
             const uint32_t depth = s_depth[g], id = (uint32_t)(base + g);
             if (kRefOrder) {
                 keys_unsorted[s] = ((uint64_t)tile << 32) | depth;
                 vals_unsorted[s] = id;
             }
             words[s_base[tile] + atomicAdd(&s_rank[tile], 1u)] = ((uint64_t)depth << 32) | id;   // any order inside the share
-        }
+        });
         return;
     }
     for (uint32_t s = block_start + t; s < block_end; s += kScatterThreads) {
