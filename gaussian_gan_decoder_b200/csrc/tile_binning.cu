@@ -233,9 +233,17 @@ tile_scatter_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ me
         };
         walk([&](int, uint32_t, uint32_t tile) { atomicAdd(&s_base[tile], 1u); });
         __syncthreads();
-        for (int i = t; i < hist_tiles; i += kScatterThreads) {
-            const uint32_t c = s_base[i];
-            if (c) s_base[i] = atomicAdd(cursors + (size_t)i * kTileCountStride + 2, c);   // the CTA's base in the tile's segment
+        // the CTA's base in every tile's segment; four claims in flight per thread (each waits ~700 clocks for its return value)
+        for (int i0 = t; i0 < hist_tiles; i0 += 4 * kScatterThreads) {
+            uint32_t c[4], b[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const int i = i0 + u * kScatterThreads; c[u] = i < hist_tiles ? s_base[i] : 0u; }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                b[u] = c[u] ? atomicAdd(cursors + (size_t)(i0 + u * kScatterThreads) * kTileCountStride + 2, c[u]) : 0u;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c[u]) s_base[i0 + u * kScatterThreads] = b[u];
         }
         __syncthreads();
         walk([&](int g, uint32_t s, uint32_t tile) {
