@@ -119,7 +119,9 @@ int ggd_decode_backward(void* stream, const ggd_decoder_config* cfg, const float
     DecodeBwdArgs a;
     if (int e = check_cfg(cfg, &a.L)) return e;
     if (P <= 0) { set_error("P must be positive (got %d)", P); return GGD_E_INVALID; }
-    if (!planes_cl_f32 || !xyz || !flat_params || !packed_f32 || !scratch || !dflat) { set_error("ggd_decode_backward: null required pointer"); return GGD_E_INVALID; }
+    // the tensor-core chain samples the fp16 planes when they are given and then never touches the fp32 ones
+    const bool f32_planes_unused = cfg && cfg->precision == 1 && cfg->pos_freqs == 0 && planes_cl_f16 != nullptr;
+    if ((!planes_cl_f32 && !f32_planes_unused) || !xyz || !flat_params || !packed_f32 || !scratch || !dflat) { set_error("ggd_decode_backward: null required pointer"); return GGD_E_INVALID; }
     if (a.L.variant != 0 && (!out_xyz || !out_scale || !out_rotation || !out_opacity || !out_color)) { set_error("ggd_decode_backward: chained variants need the forward results"); return GGD_E_INVALID; }
     const size_t need = ggd_decode_backward_scratch_bytes(cfg, P);
     if (scratch_bytes < need) { set_error("ggd_decode_backward: scratch too small (%zu < %zu)", scratch_bytes, need); return GGD_E_CAPACITY; }

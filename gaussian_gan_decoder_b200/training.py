@@ -115,7 +115,10 @@ class TrainPipeline:
             nbytes = lib.ggd_decode_backward_scratch_bytes(C.byref(cfg), P)
             self.scratch = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
         planes_nchw = planes_nchw.contiguous()
-        check(lib.ggd_planes_channels_last(s, C.byref(cfg32), p(planes_nchw), p(self.planes32)))
+        # the tensor-core backward chain samples the fp16 planes of the forward: no fp32 copy needed then
+        need_f32 = not (cfg.precision == 1 and cfg.pos_freqs == 0)
+        if need_f32:
+            check(lib.ggd_planes_channels_last(s, C.byref(cfg32), p(planes_nchw), p(self.planes32)))
         if cfg.precision == 1:
             check(lib.ggd_planes_channels_last(s, C.byref(cfg), p(planes_nchw), p(self.planes16)))
         o, a, g = self.out, self.act, self.g
@@ -147,7 +150,7 @@ class TrainPipeline:
         check(lib.ggd_activation_backward(s, P, p(a["scale"]), p(o["rotation"]), p(a["opacity"]),
                                           p(g["scale"]), p(g["rot"]), p(g["opacity"])))
         # decoder backward straight into the flat gradient buffer the parameters' .grad tensors view
-        check(lib.ggd_decode_backward(s, C.byref(cfg), p(self.planes32), p(self.planes16) if cfg.precision == 1 else None, p(xyz), P, p(flat.flat), p(flat.packed_weights_for(cfg32)),
+        check(lib.ggd_decode_backward(s, C.byref(cfg), p(self.planes32) if need_f32 else None, p(self.planes16) if cfg.precision == 1 else None, p(xyz), P, p(flat.flat), p(flat.packed_weights_for(cfg32)),
                                       p(o["xyz"]), p(o["scale"]), p(o["rotation"]), p(o["opacity"]), p(o["color"]),
                                       p(g["mean3D"]), p(g["scale"]), p(g["rot"]), p(g["opacity"]), p(g["sh"]),
                                       p(self.scratch), self.scratch.numel(), p(flat.flat_grad), None))
@@ -199,4 +202,18 @@ class TrainPipeline:
         over = R > self.capacity
         if over:
             self._alloc(int(R * 1.25) + 4096)
+        if self.bin_mode:       # as FramePipeline.check: once a step was binned per tile, stop enqueueing the radix kernels
+            C, check, ptr = self.C, self._lib.check, self._lib.ptr
+            st, info = (C.c_uint32 * 2)(), (C.c_uint32 * 2)()
+            s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            check(self.lib.ggd_raster_status(s, ptr(self.geom), self.P, st))
+            check(self.lib.ggd_raster_binning_info(s, ptr(self.geom), self.P, info))
+            if st[1] & 8:        # depths too clustered for the per-tile sort: this scene needs the radix sort
+                self.bin_mode, over = 0, True
+            elif st[1] & 2:      # mode 2 met a frame that needed the radix kernels
+                self.bin_mode, over = 1, True
+            elif self.bin_mode == 1 and info[0] and not over:
+                self.bin_mode = 2
+            elif self.bin_mode == 1 and not info[0] and not over:
+                self.bin_mode = 0
         return R, over

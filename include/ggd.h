@@ -324,7 +324,8 @@ GGD_API int ggd_mlp_forward(void* stream, const float* tri_features, const float
  * (main/decoder_models/base_decoder.py:21-27 x5, parallel_decoder.py:58-80 and
  * the sequential variants) and grid_sample backward.  No gradient flows to
  * init_position, as in the reference (it is an input).
- *   planes_cl_f32 : fp32 channels-last planes (ggd_planes_channels_last, precision 0)
+ *   planes_cl_f32 : fp32 channels-last planes (ggd_planes_channels_last, precision 0); may be NULL when planes_cl_f16 is
+ *                   given and the tensor-core chain runs (precision 1, pos_freqs 0): it reads only the fp16 planes
  *   planes_cl_f16 : optional (may be NULL): the fp16 channels-last planes the fp16 forward sampled (precision 1).  The
  *                   tensor-core chain then recomputes the forward from exactly what the forward read, at half the bytes
  *                   (measured: its plane sampling drops from 29 % of the kernel to 5 %); ignored by the fp32 chain
