@@ -34,6 +34,7 @@
 // the decision is made on the device (counters[4]) and both sets of kernels are always enqueued, the
 // ones that do not apply return at once, so no host round trip is needed.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace ggd {
 namespace {
@@ -556,6 +557,17 @@ __device__ __forceinline__ void coarse_scan(const uint32_t* __restrict__ s_c, ui
     }
 }
 
+// largest c in [1, kCoarse] with cstart[c] <= limit (cstart: the exclusive prefix above, non-decreasing); 1 if there is none
+__device__ __forceinline__ uint32_t bins_below(const uint32_t* __restrict__ cstart, uint32_t limit)
+{
+    uint32_t lo = 1, hi = kCoarse;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi + 1) >> 1;
+        if (cstart[mid] <= limit) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
 // kFromShared: the n words wait in s_out[0..n) (gathered there by the caller) instead of words[begin..]
 template <int E, bool kFromShared = false>
 __device__ __forceinline__ void dist_sort_tile(uint64_t* __restrict__ s_out, uint32_t* __restrict__ s_hist,
@@ -675,14 +687,23 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ 
 }
 
 // First round of a lazily sorted frame (lean pipelines on large images, see tile_sort_large_kernel's `lazy`): for every long
-// list, the nearest depth chunk — the leading coarse bins holding about kLazyWords words — is gathered into shared memory
-// and sorted there with the small lists' routine; its length goes to word 7 of the tile's record.  Three passes over the
-// list (depth interval, coarse histogram, gather) that wait for L2 / DRAM most of the time: 256-thread CTAs, four per SM,
-// so that several lists are in flight on an SM (the 1024-thread kernel did this round at one list per SM: 2.5 ms on the
-// 2048^2 / 2 M frame).  A list whose first coarse bin alone holds more than kLazyWords words gets length 0: the blend then marks
-// the tile and the second round sorts it completely.
+// list, the nearest depth chunk — a depth prefix of about kLazyWords words — is gathered into shared memory and sorted there
+// with the small lists' routine; its length goes to word 7 of the tile's record.  ONE pass over the whole list:
+//   1. a systematic sample (32 consecutive words out of every 32 S, at most kTileSortMax of them) gives the depth interval
+//      and a coarse histogram, hence a depth bound below which about kLazyGather words are expected;
+//   2. the pass over the list gathers every word below that bound into shared memory (room for kTileSortMax);
+//   3. if more than kLazyWords arrived, an exact coarse histogram of the gathered words (shared memory only) trims them to
+//      the leading bins that hold at most kLazyWords.
+// Both cuts are monotone in the depth ("depth < bound", "coarse bin of the depth < c"), so the chunk is a prefix of the sorted
+// list, ties included.  (Before: three passes over the list — interval, histogram, gather — and one shared-memory atomic per
+// gathered word: 1.26 ms on the 2048^2 / 2 M frame, now 1.0.)
+// 256-thread CTAs, four per SM, so that several lists are in flight on an SM.  A list whose gather overflows the buffer, or
+// whose first bin alone holds more than kLazyWords words, gets length 0: the blend then marks the tile and the second round
+// sorts it completely.
 constexpr uint32_t kLazyWords = 2048;      // 2048^2 / 2 M frame: 1024 -> 12.0 ms (too many second rounds), 2048 -> 7.1, 4096 -> 7.3, 8192 -> 7.9
+constexpr uint32_t kLazyGather = 2816;     // expected words of the gather: kLazyWords + head room for the trim, 1280 below the buffer's end for the sample's error
 static_assert(kLazyWords == 8 * kTileSortThreads, "tile_sort_lazy_kernel sorts its chunk with dist_sort_tile<8>");
+static_assert(2 * kLazyWords == kTileSortMax, "the trim compacts into the histogram array, which holds kTileSortMax / 2 words");
 __global__ void __launch_bounds__(kTileSortThreads, 4)
 tile_sort_lazy_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ words, uint64_t* __restrict__ keys,
                       uint32_t* __restrict__ vals, const uint32_t* __restrict__ counters, uint32_t* __restrict__ recs)
@@ -691,32 +712,15 @@ tile_sort_lazy_kernel(const uint2* __restrict__ ranges, const uint64_t* __restri
     extern __shared__ __align__(16) uint8_t s_dyn[];
     uint64_t* s = reinterpret_cast<uint64_t*>(s_dyn);                              // [kTileSortMax]
     uint32_t* h = reinterpret_cast<uint32_t*>(s_dyn + sizeof(uint64_t) * kTileSortMax);   // [kTileSortMax]
+    uint64_t* h64 = reinterpret_cast<uint64_t*>(h);                                // [kTileSortMax / 2] during the trim
     __shared__ uint32_t s_red[2][kTileSortThreads / 32];
     __shared__ uint32_t s_c[kCoarse], s_cstart[kCoarse + 1];
     __shared__ uint32_t s_n;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t n_large = __ldg(counters + 7);
-    constexpr int kWalk = 8;
-    for (uint32_t li = blockIdx.x; li < n_large; li += gridDim.x) {
-        const uint32_t tile = recs[(size_t)li * kTileCountStride + 1];
-        const uint2 range = ranges[tile];
-        const uint32_t n = range.y - range.x;
-        const uint64_t* src = words + range.x;
-        auto walk = [&](auto&& use) {
-            for (uint32_t i0 = t; i0 < n; i0 += kWalk * kTileSortThreads) {
-                uint64_t w[kWalk];
-#pragma unroll
-                for (int k = 0; k < kWalk; ++k) {
-                    const uint32_t i = i0 + (uint32_t)k * kTileSortThreads;
-                    w[k] = i < n ? __ldg(src + i) : 0ull;
-                }
-#pragma unroll
-                for (int k = 0; k < kWalk; ++k)
-                    if (i0 + (uint32_t)k * kTileSortThreads < n) use(w[k]);
-            }
-        };
-        uint32_t dmin = 0xffffffffu, dmax = 0u;
-        walk([&](uint64_t w) { const uint32_t d = (uint32_t)(w >> 32); dmin = min(dmin, d); dmax = max(dmax, d); });
+    constexpr int kWalk = 8;                 // loads in flight per thread
+    // CTA-wide min / max of a depth pair (every thread gets the result); also clears the coarse bins and the gather counter
+    auto interval = [&](uint32_t& dmin, uint32_t& dmax) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             dmin = min(dmin, __shfl_xor_sync(0xffffffffu, dmin, o));
@@ -727,22 +731,103 @@ tile_sort_lazy_kernel(const uint2* __restrict__ ranges, const uint64_t* __restri
         if (t == 0) s_n = 0;
         __syncthreads();
         for (int k = 0; k < kTileSortThreads / 32; ++k) { dmin = min(dmin, s_red[0][k]); dmax = max(dmax, s_red[1][k]); }
-        const float scale_c = (float)kCoarse / ((float)(dmax - dmin) + 1.0f);
-        auto coarse_of = [&](uint64_t w) { return min((uint32_t)(kCoarse - 1), (uint32_t)((float)((uint32_t)(w >> 32) - dmin) * scale_c)); };
-        walk([&](uint64_t w) { atomicAdd(&s_c[coarse_of(w)], 1u); });
+    };
+    for (uint32_t li = blockIdx.x; li < n_large; li += gridDim.x) {
+        const uint32_t tile = recs[(size_t)li * kTileCountStride + 1];
+        const uint2 range = ranges[tile];
+        const uint32_t n = range.y - range.x;
+        const uint64_t* src = words + range.x;
+        auto fail = [&]() {                           // (uniform) left to the second round
+            if (t == 0) recs[(size_t)tile * kTileCountStride + 7] = 0u;
+            __syncthreads();
+        };
+        // ---- 1. the sample: depth bits of words [32 S j, 32 S j + 32), j = 0, 1, ... into h ----
+        const uint32_t S = max(4u, (n + kTileSortMax - 1) / kTileSortMax);
+        const uint32_t full = n / (32u * S), rest = min(32u, n - full * 32u * S);
+        const uint32_t n_s = full * 32u + rest;       // <= kTileSortMax
+        uint32_t dmin = 0xffffffffu, dmax = 0u;
+        for (uint32_t v0 = t; v0 < n_s; v0 += kWalk * kTileSortThreads) {
+            uint32_t d[kWalk];
+#pragma unroll
+            for (int k = 0; k < kWalk; ++k) {
+                const uint32_t v = v0 + (uint32_t)k * kTileSortThreads;
+                d[k] = v < n_s ? (uint32_t)(__ldg(src + (size_t)(v >> 5) * 32u * S + (v & 31u)) >> 32) : 0u;
+            }
+#pragma unroll
+            for (int k = 0; k < kWalk; ++k) {
+                const uint32_t v = v0 + (uint32_t)k * kTileSortThreads;
+                if (v < n_s) { h[v] = d[k]; dmin = min(dmin, d[k]); dmax = max(dmax, d[k]); }
+            }
+        }
+        interval(dmin, dmax);
+        const float span = (float)(dmax - dmin) + 1.0f, scale_c = (float)kCoarse / span;
+        for (uint32_t v = t; v < n_s; v += kTileSortThreads)
+            atomicAdd(&s_c[min((uint32_t)(kCoarse - 1), (uint32_t)((float)(h[v] - dmin) * scale_c))], 1u);
         __syncthreads();
         coarse_scan(s_c, s_cstart);
         __syncthreads();
-        uint32_t c1 = 1;
-        while (c1 < (uint32_t)kCoarse && s_cstart[c1 + 1] <= kLazyWords) ++c1;
-        const uint32_t m = s_cstart[c1];
-        if (m > kLazyWords) {                         // (uniform) the first bin alone is too long for this kernel
-            if (t == 0) recs[(size_t)tile * kTileCountStride + 7] = 0u;
-            __syncthreads();
-            continue;
+        // sampled words wanted below the bound -> number of leading bins -> the bound in depth bits (any bound cuts a prefix)
+        const uint32_t c1 = bins_below(s_cstart, (uint32_t)((float)kLazyGather * (float)n_s / (float)n));
+        const uint32_t bound = c1 == (uint32_t)kCoarse ? 0xffffffffu : dmin + (uint32_t)((float)c1 * span * (1.0f / (float)kCoarse));
+        // ---- 2. one pass over the list: gather the words below the bound (places claimed once per warp and step) ----
+        for (uint32_t base = 0; base < n; base += kWalk * kTileSortThreads) {
+            uint64_t w[kWalk];
+#pragma unroll
+            for (int k = 0; k < kWalk; ++k) {
+                const uint32_t i = base + (uint32_t)(k * kTileSortThreads + t);
+                w[k] = i < n ? __ldg(src + i) : ~0ull;
+            }
+            uint32_t cnt = 0;
+#pragma unroll
+            for (int k = 0; k < kWalk; ++k) cnt += (uint32_t)(w[k] >> 32) < bound ? 1u : 0u;
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += u;
+            }
+            uint32_t at = 0;
+            if (lane == 31) at = atomicAdd(&s_n, incl);
+            at = __shfl_sync(0xffffffffu, at, 31) + incl - cnt;
+#pragma unroll
+            for (int k = 0; k < kWalk; ++k)
+                if ((uint32_t)(w[k] >> 32) < bound) {
+                    if (at < kTileSortMax) s[at] = w[k];
+                    ++at;
+                }
         }
-        walk([&](uint64_t w) { if (coarse_of(w) < c1) s[atomicAdd(&s_n, 1u)] = w; });
         __syncthreads();
+        uint32_t m = s_n;
+        __syncthreads();                              // (interval() clears s_n: below, or at the next list)
+        if (m > kTileSortMax || m == 0) { fail(); continue; }
+        if (m > kLazyWords) {
+            // ---- 3. trim to the leading bins of an exact histogram of the gathered words ----
+            uint32_t gmin = 0xffffffffu, gmax = 0u;
+            for (uint32_t i = t; i < m; i += kTileSortThreads) { const uint32_t d = (uint32_t)(s[i] >> 32); gmin = min(gmin, d); gmax = max(gmax, d); }
+            interval(gmin, gmax);
+            const float scale_g = (float)kCoarse / ((float)(gmax - gmin) + 1.0f);
+            auto coarse_g = [&](uint64_t w) { return min((uint32_t)(kCoarse - 1), (uint32_t)((float)((uint32_t)(w >> 32) - gmin) * scale_g)); };
+            for (uint32_t i = t; i < m; i += kTileSortThreads) atomicAdd(&s_c[coarse_g(s[i])], 1u);
+            __syncthreads();
+            coarse_scan(s_c, s_cstart);
+            __syncthreads();
+            const uint32_t c2 = bins_below(s_cstart, kLazyWords), m2 = s_cstart[c2];
+            if (m2 > kLazyWords) { fail(); continue; }         // the first bin alone is too long for this kernel
+            for (uint32_t base = 0; base < m; base += kTileSortThreads) {
+                const uint32_t i = base + t;
+                const uint64_t w = i < m ? s[i] : 0ull;
+                const bool keep = i < m && coarse_g(w) < c2;
+                const uint32_t mask = __ballot_sync(0xffffffffu, keep);
+                uint32_t at = 0;
+                if (lane == 0 && mask) at = atomicAdd(&s_n, (uint32_t)__popc(mask));
+                at = __shfl_sync(0xffffffffu, at, 0);
+                if (keep) h64[at + __popc(mask & ((1u << lane) - 1u))] = w;
+            }
+            __syncthreads();
+            for (uint32_t i = t; i < m2; i += kTileSortThreads) s[i] = h64[i];
+            m = m2;
+            __syncthreads();
+        }
         if (m <= 256) dist_sort_tile<1, true>(s, h, nullptr, range.x, m, tile, keys, vals);
         else if (m <= 512) dist_sort_tile<2, true>(s, h, nullptr, range.x, m, tile, keys, vals);
         else if (m <= 1024) dist_sort_tile<4, true>(s, h, nullptr, range.x, m, tile, keys, vals);
