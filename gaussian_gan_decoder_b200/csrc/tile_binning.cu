@@ -442,13 +442,16 @@ constexpr int kTileSortThreads = 256;
 // Bitonic sort of n_pad = 256 * E words, E consecutive words per thread ("blocked"): compare distances
 // below E stay inside a thread's registers, distances below 32 E are warp shuffles, and only the three
 // largest distances (6 of the network's stages, whatever n_pad is) go through shared memory.
-template <int E>
+template <int E, bool kFromShared = false>      // kFromShared: the words already wait in s[0..n)
 __device__ __forceinline__ void sort_tile(uint64_t* __restrict__ s, const uint64_t* __restrict__ words, uint32_t begin,
                                           uint32_t n, uint32_t tile, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
 {
     constexpr uint32_t n_pad = kTileSortThreads * E;
     const int t = threadIdx.x;
-    for (uint32_t i = t; i < n_pad; i += kTileSortThreads) s[i] = i < n ? __ldg(words + begin + i) : ~0ull;
+    for (uint32_t i = t; i < n_pad; i += kTileSortThreads) {
+        if (i >= n) s[i] = ~0ull;
+        else if (!kFromShared) s[i] = __ldg(words + begin + i);
+    }
     __syncthreads();
     uint64_t v[E];
 #pragma unroll
@@ -632,7 +635,7 @@ __device__ __forceinline__ void dist_sort_tile(uint64_t* __restrict__ s_out, uin
 #pragma unroll
     for (int k = 0; k < kTileSortThreads / 32; ++k) if (k < warp) start += s_part[k];
     if (overfull) {   // uniform for the CTA
-        sort_tile<E>(s_out, words, begin, n, tile, keys, vals);
+        sort_tile<E, kFromShared>(s_out, words, begin, n, tile, keys, vals);
         return;
     }
     {

@@ -276,16 +276,32 @@ def test_super_tile_scatter_bit_exact(cuda, monkeypatch, P, W, H, trained):
     assert torch.equal(other["out_color"], ours["out_color"]) and torch.equal(other["point_list"], ours["point_list"])
 
 
-@pytest.mark.parametrize("backward", [False, True])
-def test_lean_large_image_sorts_lazily_same_frame(cuda, backward):
+@pytest.mark.parametrize("backward,scene", [(False, "head"), (True, "head"), (False, "depth_layers"), (False, "index_by_depth")])
+def test_lean_large_image_sorts_lazily_same_frame(cuda, backward, scene):
     """GGD_BINNING_LEAN on an image beyond 1024^2: long tile lists are sorted only in their nearest depth chunk, the blend
     marks the tiles that did not saturate inside it, those are sorted completely and blended again.  Image, final T and
     contributor counts must be the bits of the complete path, and the backward (which replays the lists from the last
-    contributor) must see the same gradients."""
+    contributor) must see the same gradients.
+    The chunk's depth bound comes from a sample of the list: `depth_layers` puts every Gaussian on one of three depths (a
+    bound then takes a whole layer or nothing: the chunk overflows or is empty and the tile goes to the second round),
+    `index_by_depth` orders the Gaussians, hence the unsorted lists, by depth (a sample taken at regular places of the list
+    must still see the whole interval)."""
     from gaussian_gan_decoder_b200 import rasterizer as rz
     _C = rz._C
     P, S = 1_500_000, 1040                                 # 65 x 65 tiles, ~13k instances per tile
-    s = to_dev(synthetic.raster_scene(P, size=S, fov_deg=12.0, seed_offset=77), cuda)
+    s = synthetic.raster_scene(P, size=S, fov_deg=12.0, seed_offset=77)
+    if scene != "head":
+        V = s["viewmatrix"]
+        d = V[:3, 2] / V[:3, 2].norm()
+        z = s["means3D"] @ d
+        if scene == "depth_layers":
+            layer = torch.bucketize(z, torch.quantile(z[::97], torch.tensor([1 / 3, 2 / 3])))
+            target = torch.stack([z[layer == k].mean() for k in range(3)])[layer]
+            s["means3D"] = (s["means3D"] + (target - z)[:, None] * d[None, :]).contiguous()
+        else:
+            order = torch.argsort(z)
+            s = {k: (v[order].contiguous() if torch.is_tensor(v) and v.dim() > 0 and v.shape[0] == P else v) for k, v in s.items()}
+    s = to_dev(s, cuda)
     e = torch.empty(0, device=cuda)
 
     def run(keep):
