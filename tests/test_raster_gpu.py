@@ -276,7 +276,50 @@ def test_super_tile_scatter_bit_exact(cuda, monkeypatch, P, W, H, trained):
     assert torch.equal(other["out_color"], ours["out_color"]) and torch.equal(other["point_list"], ours["point_list"])
 
 
-@pytest.mark.parametrize("backward,scene", [(False, "head"), (True, "head"), (False, "depth_layers"), (False, "index_by_depth")])
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("W,H", [(1100, 1050), (2050, 520)])
+def test_bit_exact_large_image_mixed_splat_sizes(cuda, W, H):
+    """Beyond 4096 tiles the frame takes the difference-array tile counting, the super-tile scatter and (lean binding) the
+    lazy sort by itself.  Image sides that are no multiple of 16 (nor of the 128-pixel super-tiles), a few hundred splats
+    that cover most of the image next to needle-like and ordinary ones: every output keeps the reference's bits, and the
+    lean binding renders the same frame."""
+    from gaussian_gan_decoder_b200 import rasterizer as rz
+    P = 300_000
+    s = synthetic.raster_scene(P, size=max(W, H), fov_deg=13.0, seed_offset=W)
+    g = synthetic.gen(W + H)
+    scales = s["scales"].clone()
+    scales[:300] = torch.exp(-1.2 + 0.4 * torch.randn(300, 3, generator=g))                  # cover hundreds to thousands of tiles
+    scales[300:20_300] = torch.exp(-5.0 + 2.0 * torch.randn(20_000, 3, generator=g)).clamp(max=0.3)   # needles
+    s["scales"] = scales
+    op = s["opacities"].clone()
+    op[:300] = 0.02 + 0.1 * torch.rand(300, 1, generator=g)                                   # faint: the lists stay long
+    s["opacities"] = op
+    s = to_dev(s, cuda)
+    s["W"], s["H"] = W, H
+    assert ((W + 15) // 16) * ((H + 15) // 16) > 4096
+    ref = RefCuda().forward(s, cuda)
+    ours = run_ours(s, cuda)
+    info = (C.c_uint32 * 2)()
+    _lib.check(_lib.load().ggd_raster_binning_info(None, C.c_void_p(ours["_buffers"][0].data_ptr()), P, info))
+    assert info[0] == 1 and info[1] > 4096, tuple(info)        # per-tile path with long lists
+    assert ref["R"] > 20 * P
+    assert_bit_exact(ours, ref, P)
+    old = rz.keep_reference_order_arrays
+    rz.keep_reference_order_arrays = False
+    try:
+        e = torch.empty(0, device=cuda)
+        lean = rz._C.rasterize_gaussians(s["bg"], s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e, s["viewmatrix"],
+                                         s["projmatrix"], s["tanfovx"], s["tanfovy"], H, W, s["shs"], 0, s["campos"], False, False)
+    finally:
+        rz.keep_reference_order_arrays = old
+    assert lean[0] == ours["R"] and torch.equal(lean[1], ours["out_color"]) and torch.equal(lean[2], ours["radii"])
+    cap = getattr(lean[4], "ggd_capacity", 0)
+    for name, dt in (("accum_alpha", torch.float32), ("n_contrib", torch.int32)):
+        assert torch.equal(rz.field(lean[5], 2, name, P, W, H, cap, dt), ours[name]), name
+
+
+@pytest.mark.parametrize("backward,scene", [(False, "head"), (True, "head"), (False, "depth_layers"), (True, "depth_layers"), (False, "index_by_depth"),
+                                            (False, "head_longer_lists")])
 def test_lean_large_image_sorts_lazily_same_frame(cuda, backward, scene):
     """GGD_BINNING_LEAN on an image beyond 1024^2: long tile lists are sorted only in their nearest depth chunk, the blend
     marks the tiles that did not saturate inside it, those are sorted completely and blended again.  Image, final T and
@@ -285,12 +328,13 @@ def test_lean_large_image_sorts_lazily_same_frame(cuda, backward, scene):
     The chunk's depth bound comes from a sample of the list: `depth_layers` puts every Gaussian on one of three depths (a
     bound then takes a whole layer or nothing: the chunk overflows or is empty and the tile goes to the second round),
     `index_by_depth` orders the Gaussians, hence the unsorted lists, by depth (a sample taken at regular places of the list
-    must still see the whole interval)."""
+    must still see the whole interval), `head_longer_lists` zooms in until lists pass 4 x 4096 words (the sample then takes
+    less than a quarter of a list)."""
     from gaussian_gan_decoder_b200 import rasterizer as rz
     _C = rz._C
     P, S = 1_500_000, 1040                                 # 65 x 65 tiles, ~13k instances per tile
-    s = synthetic.raster_scene(P, size=S, fov_deg=12.0, seed_offset=77)
-    if scene != "head":
+    s = synthetic.raster_scene(P, size=S, fov_deg=9.0 if scene == "head_longer_lists" else 12.0, seed_offset=77)
+    if scene in ("depth_layers", "index_by_depth"):
         V = s["viewmatrix"]
         d = V[:3, 2] / V[:3, 2].norm()
         z = s["means3D"] @ d
@@ -318,7 +362,7 @@ def test_lean_large_image_sorts_lazily_same_frame(cuda, backward, scene):
     R, cap = full[0], getattr(full[4], "ggd_capacity", 0)
     info = (C.c_uint32 * 2)()
     _lib.check(_lib.load().ggd_raster_binning_info(None, _lib.ptr(lean[3]), P, info))
-    assert info[0] == 1 and info[1] > 3 * 4096, tuple(info)           # binned per tile, lists long enough for the lazy path
+    assert info[0] == 1 and info[1] > (4 if scene == "head_longer_lists" else 3) * 4096, tuple(info)   # binned per tile, lists long enough for the lazy path
     assert lean[0] == R and torch.equal(lean[1], full[1]) and torch.equal(lean[2], full[2])
     for name, dt in (("accum_alpha", torch.float32), ("n_contrib", torch.int32), ("ranges", torch.int32)):
         a = rz.field(full[5], 2, name, P, S, S, cap, dt)
