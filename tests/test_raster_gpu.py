@@ -277,7 +277,7 @@ def test_super_tile_scatter_bit_exact(cuda, monkeypatch, P, W, H, trained):
 
 
 @pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
-@pytest.mark.parametrize("W,H", [(1100, 1050), (2050, 520)])
+@pytest.mark.parametrize("W,H", [(1100, 1050), (2050, 520), (2100, 2100), (4100, 600)])      # the third: more than 16 384 tiles
 def test_bit_exact_large_image_mixed_splat_sizes(cuda, W, H):
     """Beyond 4096 tiles the frame takes the difference-array tile counting, the super-tile scatter and (lean binding) the
     lazy sort by itself.  Image sides that are no multiple of 16 (nor of the 128-pixel super-tiles), a few hundred splats
