@@ -8,19 +8,28 @@
 
 namespace ggd {
 
+// Index of a sample's lower tap along an axis of n texels.  The conversion saturates for positions far outside the box
+// (INT_MAX beyond ~1e9 texels, +inf) and "index + 1" then overflows — the out-of-range tests that follow were compiled on
+// the assumption that it cannot, and a huge positive coordinate read outside the planes.  Clamped to [-2, n]: still out of
+// range on the side it was, same bits for every position whose taps touch the planes (NaN converts to 0 as before).
+__device__ __forceinline__ int tap_index(float floor_of_position, int n)
+{
+    return min(max((int)floor_of_position, -2), n);
+}
+
 // one bilinear / trilinear sample of 4 channels, zeros padding, align_corners=False
 __device__ __forceinline__ float4 sample4(const float* __restrict__ plane, int arch, int D, int H, int W,
                                           float gx, float gy, float gz, int c4)
 {
     const float ix = ((gx + 1.f) * W - 1.f) * 0.5f, iy = ((gy + 1.f) * H - 1.f) * 0.5f;
     const float fx0 = floorf(ix), fy0 = floorf(iy);
-    const int x0 = (int)fx0, y0 = (int)fy0;
+    const int x0 = tap_index(fx0, W), y0 = tap_index(fy0, H);
     const float wx1 = ix - fx0, wy1 = iy - fy0, wx0 = 1.f - wx1, wy0 = 1.f - wy1;
     int z0 = 0;
     float wz0 = 1.f, wz1 = 0.f;
     if (arch == 1) {
         const float iz = ((gz + 1.f) * D - 1.f) * 0.5f, fz0 = floorf(iz);
-        z0 = (int)fz0; wz1 = iz - fz0; wz0 = 1.f - wz1;
+        z0 = tap_index(fz0, D); wz1 = iz - fz0; wz0 = 1.f - wz1;
     }
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     const int nz = arch == 1 ? 2 : 1;
@@ -61,7 +70,7 @@ namespace ggd {
 __device__ __forceinline__ void sample_axis(float g, int n, uint32_t stride_bytes, float (&w)[2], uint32_t (&o)[2])
 {
     const float i = ((g + 1.f) * n - 1.f) * 0.5f, f0 = floorf(i);
-    const int i0 = (int)f0;
+    const int i0 = tap_index(f0, n);
     const float w1 = i - f0, w0 = 1.f - w1;
     w[0] = (unsigned)i0 < (unsigned)n ? w0 : 0.f;
     w[1] = (unsigned)(i0 + 1) < (unsigned)n ? w1 : 0.f;
@@ -115,7 +124,7 @@ struct TapColumn {
                                           float gx, float gy, float gz, int dx)
     {
         const float ix = ((gx + 1.f) * W - 1.f) * 0.5f, fx0 = floorf(ix);
-        const int xi = (int)fx0 + dx;
+        const int xi = tap_index(fx0, W) + dx;
         const float wx1 = ix - fx0, wxl = dx ? wx1 : 1.f - wx1;
         const float wx = (unsigned)xi < (unsigned)W ? wxl : 0.f;
         const char* base = plane_c8 + (uint32_t)min(max(xi, 0), W - 1) * (kFeat * 2);
@@ -156,13 +165,13 @@ __device__ __forceinline__ void scatter4(float* __restrict__ dplane /*[32*D][H][
 {
     const float ix = ((gx + 1.f) * W - 1.f) * 0.5f, iy = ((gy + 1.f) * H - 1.f) * 0.5f;
     const float fx0 = floorf(ix), fy0 = floorf(iy);
-    const int x0 = (int)fx0, y0 = (int)fy0;
+    const int x0 = tap_index(fx0, W), y0 = tap_index(fy0, H);
     const float wx1 = ix - fx0, wy1 = iy - fy0, wx0 = 1.f - wx1, wy0 = 1.f - wy1;
     int z0 = 0;
     float wz0 = 1.f, wz1 = 0.f;
     if (arch == 1) {
         const float iz = ((gz + 1.f) * D - 1.f) * 0.5f, fz0 = floorf(iz);
-        z0 = (int)fz0; wz1 = iz - fz0; wz0 = 1.f - wz1;
+        z0 = tap_index(fz0, D); wz1 = iz - fz0; wz0 = 1.f - wz1;
     }
     const size_t HW = (size_t)H * W;
     const int nz = arch == 1 ? 2 : 1;

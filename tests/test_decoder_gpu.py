@@ -106,6 +106,43 @@ def test_points_outside_and_on_the_border_of_the_planes(cuda, arch, variant, pre
 
 
 @pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("arch,posenc,variant", [("eg3d", False, "parallel"), ("panohead", True, "sequential"), ("panohead", False, "sequential")])
+def test_non_finite_and_huge_positions_stay_in_their_rows(cuda, arch, posenc, variant, precision):
+    """Positions that are NaN, infinite or astronomically far outside the box must not read outside the planes, and — every
+    point being decoded by itself — must not change any other point's attributes.  (Their own rows, and the gradients, are
+    whatever the arithmetic gives: the position is an input of the MLPs, in the reference as well.)"""
+    g = synthetic.gen(41)
+    depth = 3 if arch == "panohead" else 1
+    planes = synthetic.planes(arch, g, res=64, depth=depth).to(cuda)
+    P = 5000
+    xyz = synthetic.head_shell_points(P, g)
+    bad = xyz.clone()
+    rows = torch.arange(7, P, 131)
+    vals = torch.tensor([float("nan"), float("inf"), -float("inf"), 1e30, -1e30, 3e38, 65504.0 * 4, -2.5e9])
+    for n, r in enumerate(rows.tolist()):
+        bad[r, n % 3] = vals[n % len(vals)]
+        if n % 5 == 0:
+            bad[r] = vals[(n // 5) % len(vals)]
+    keep = torch.ones(P, dtype=torch.bool)
+    keep[rows] = False
+    torch.manual_seed(8)
+    dec = CLASSES[variant](StubG(planes, arch, depth), use_xyz_embedding=posenc, use_gen_finetune=False, device=cuda)
+    dec.precision = precision
+    with torch.no_grad():
+        clean = dec.decode(planes, xyz.to(cuda))
+        dirty = dec.decode(planes, bad.to(cuda))
+    torch.cuda.synchronize()
+    for k in clean:
+        assert torch.equal(clean[k][keep.to(cuda)], dirty[k][keep.to(cuda)]), k
+    # the backward's plane-gradient scatter walks the same taps: it must stay inside the planes as well
+    pl = planes.clone().requires_grad_(True)
+    out = dec.decode(pl, bad.to(cuda))
+    sum((out[k][keep.to(cuda)] ** 2).sum() for k in out).backward()
+    torch.cuda.synchronize()
+    assert pl.grad is not None and pl.grad.shape == planes.shape
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
 @pytest.mark.parametrize("arch,variant,posenc,hidden", [("panohead", "sequential_reverse", False, 64), ("eg3d", "parallel", True, 100),
                                                           ("eg3d", "sequential", False, 8)])
 def test_hidden_dim_below_128(cuda, arch, variant, posenc, hidden, precision):
