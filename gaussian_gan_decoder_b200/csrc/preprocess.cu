@@ -260,7 +260,11 @@ preprocess_kernel(const PreprocessArgs a, float* __restrict__ depths, int* __res
                 uint2 rmin, rmax;
                 tile_rect(pix, (int)my_radius, a.grid_x, a.grid_y, rmin, rmax);
                 const uint32_t area = (rmax.x - rmin.x) * (rmax.y - rmin.y);
-                if (area != 0) {
+                // A NaN covariance (NaN / infinite scale) gives radius (int)NaN = 0 with a one-tile rectangle.  The
+                // reference counts that tile (forward.cu:240-254) but duplicateWithKeys skips radius 0
+                // (rasterizer_impl.cu:84), so its key slot keeps whatever the buffer held; here such a Gaussian is
+                // culled.  A finite covariance has radius >= 3 (the 0.3 added to the diagonal): nothing else changes.
+                if (area != 0 && (int)my_radius > 0) {
                     if (!have_col) {
                         const float* shp = sh_staged ? (s_col + 3 * t) : (a.shs + (size_t)idx * a.M * 3);
                         V3 res = kSH0 * V3{shp[0], shp[1], shp[2]};

@@ -277,6 +277,41 @@ def test_super_tile_scatter_bit_exact(cuda, monkeypatch, P, W, H, trained):
 
 
 @pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("size", [256, 1104])
+def test_non_finite_and_absurd_gaussians_like_the_reference(cuda, size):
+    """NaN / infinite means and opacities, and splats of astronomical size (their radius saturates the int it is stored in):
+    the reference culls the former through an empty tile rectangle and spreads the latter over every tile.  Same bits
+    here, whichever binning path the image size selects.
+    NaN / infinite SCALES are left out of the comparison: the reference gives them radius (int)NaN = 0 but one touched
+    tile, and duplicateWithKeys then skips them (radius 0) — their key slots keep whatever the buffer held.  Here they are
+    culled: the frame is the frame without them (second half)."""
+    P = 30_000
+    s = synthetic.raster_scene(P, size=size, fov_deg=14.0, seed_offset=size)
+    nan, inf = float("nan"), float("inf")
+    m, sc, op = s["means3D"].clone(), s["scales"].clone(), s["opacities"].clone()
+    m[10] = nan; m[11, 0] = inf; m[12, 2] = -inf; m[13, 1] = 1e30; m[14] = torch.tensor([1e20, -1e20, 1e20])
+    sc[22] = 1e10; sc[23, 1] = 1e5; sc[24] = 0.0; sc[25] = torch.tensor([3e3, 1e-9, 2.0]); sc[26] = 40.0
+    op[30] = nan; op[31] = inf; op[32] = -1.0; op[33] = 0.0; op[22] = 0.05; op[23] = 0.05; op[25] = 0.05; op[26] = 0.03
+    s["means3D"], s["scales"], s["opacities"] = m, sc, op
+    s = to_dev(s, cuda)
+    ref = RefCuda().forward(s, cuda)
+    ours = run_ours(s, cuda)
+    assert ref["R"] > 0
+    assert_bit_exact(ours, ref, P)
+    sc = s["scales"].clone()
+    sc[20] = nan; sc[21, 0] = inf
+    s["scales"] = sc
+    worse = run_ours(s, cuda)
+    assert worse["R"] == ours["R"] - int(ours["tiles_touched"][20]) - int(ours["tiles_touched"][21])
+    assert int(worse["radii"][20]) == 0 and int(worse["tiles_touched"][20]) == 0 and int(worse["tiles_touched"][21]) == 0
+    gone = torch.ones(P, dtype=torch.bool, device=cuda)
+    gone[20:22] = False
+    without = {k: (v[gone].contiguous() if torch.is_tensor(v) and v.dim() > 0 and v.shape[0] == P else v) for k, v in s.items()}
+    expect = run_ours(without, cuda)
+    assert torch.equal(worse["out_color"], expect["out_color"]) and torch.equal(worse["n_contrib"], expect["n_contrib"])
+
+
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
 @pytest.mark.parametrize("W,H", [(1100, 1050), (2050, 520), (2100, 2100), (4100, 600)])      # the third: more than 16 384 tiles
 def test_bit_exact_large_image_mixed_splat_sizes(cuda, W, H):
     """Beyond 4096 tiles the frame takes the difference-array tile counting, the super-tile scatter and (lean binding) the
