@@ -106,6 +106,33 @@ def test_points_outside_and_on_the_border_of_the_planes(cuda, arch, variant, pre
 
 
 @pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("arch,depth,H,W", [("eg3d", 1, 48, 80), ("panohead", 3, 72, 40), ("panohead", 5, 33, 57), ("eg3d", 1, 1, 1)])
+def test_non_square_planes_and_other_grid_depths(cuda, arch, depth, H, W, precision):
+    """The reference's planes are 256 x 256 (x 3 for the tri-grid), but grid_sample takes any extent: other heights, widths
+    and grid depths, odd sizes and the one-texel plane, forward and plane gradient against the oracle."""
+    g = synthetic.gen(H * W + depth)
+    planes = torch.randn(1, 3, 32 * depth, H, W, generator=g)
+    xyz = torch.cat([synthetic.head_shell_points(3000, g), (torch.rand(1000, 3, generator=g) - 0.5) * 1.3]).contiguous()
+    torch.manual_seed(H + W)
+    dec = CLASSES["sequential"](StubG(planes.to(cuda), arch, depth), use_xyz_embedding=False, use_gen_finetune=False, device=cuda)
+    dec.precision = precision
+    flat = torch.cat([p.detach().reshape(-1).cpu() for p in dec.get_params_custom()])
+    with torch.no_grad():
+        out = dec.decode(planes.to(cuda), xyz.to(cuda))
+        ref = do.decode(arch, "sequential", 0, flat, planes, xyz, 1.0, depth)
+    check(out, ref, precision)
+    pl = planes.to(cuda).requires_grad_(True)
+    got = dec.decode(pl, xyz.to(cuda))
+    keys = ("xyz", "scale", "rotation", "opacity", "color")
+    sum((got[k] ** 2).sum() for k in keys).backward()
+    plr = planes.clone().requires_grad_(True)
+    want = do.decode(arch, "sequential", 0, flat, plr, xyz, 1.0, depth)
+    sum((want[k] ** 2).sum() for k in keys).backward()
+    scale = float(plr.grad.abs().max()) + 1e-30
+    assert float((pl.grad.cpu() - plr.grad).abs().max()) <= (2e-2 if precision == "fp16" else 2e-4) * scale
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
 @pytest.mark.parametrize("arch,posenc,variant", [("eg3d", False, "parallel"), ("panohead", True, "sequential"), ("panohead", False, "sequential")])
 def test_non_finite_and_huge_positions_stay_in_their_rows(cuda, arch, posenc, variant, precision):
     """Positions that are NaN, infinite or astronomically far outside the box must not read outside the planes, and — every
