@@ -106,6 +106,28 @@ def test_points_outside_and_on_the_border_of_the_planes(cuda, arch, variant, pre
 
 
 @pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("arch,box_warp", [("panohead", 0.7), ("eg3d", 2.3)])
+def test_box_warp_other_than_one(cuda, arch, box_warp, precision):
+    """rendering_kwargs['box_warp'] scales the positions before sampling (2 / box_warp: renderer.py:59 / PanoHead :49); the
+    released PanoHead configuration uses 0.7, every other test here 1.0.  With 0.7 part of the shell falls outside the planes."""
+    g = synthetic.gen(31)
+    depth = 3 if arch == "panohead" else 1
+    planes = synthetic.planes(arch, g, res=64, depth=depth)
+    xyz = synthetic.head_shell_points(6000, g)
+    torch.manual_seed(12)
+    dec = CLASSES["sequential_reverse"](StubG(planes.to(cuda), arch, depth, box_warp=box_warp), use_xyz_embedding=True, use_gen_finetune=False,
+                                        device=cuda)
+    dec.precision = precision
+    flat = torch.cat([p.detach().reshape(-1).cpu() for p in dec.get_params_custom()])
+    with torch.no_grad():
+        out = dec.decode(planes.to(cuda), xyz.to(cuda))
+        ref = do.decode(arch, "sequential_reverse", 10, flat, planes, xyz, box_warp, depth)
+        one = do.decode(arch, "sequential_reverse", 10, flat, planes, xyz, 1.0, depth)
+    assert float((ref["color"] - one["color"]).abs().max()) > 1e-3        # the factor matters in this scene
+    check(out, ref, precision)
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
 @pytest.mark.parametrize("arch,depth,H,W", [("eg3d", 1, 48, 80), ("panohead", 3, 72, 40), ("panohead", 5, 33, 57), ("eg3d", 1, 1, 1)])
 def test_non_square_planes_and_other_grid_depths(cuda, arch, depth, H, W, precision):
     """The reference's planes are 256 x 256 (x 3 for the tri-grid), but grid_sample takes any extent: other heights, widths
