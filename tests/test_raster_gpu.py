@@ -277,6 +277,30 @@ def test_super_tile_scatter_bit_exact(cuda, monkeypatch, P, W, H, trained):
 
 
 @pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
+@pytest.mark.parametrize("size,offset", [(256, 0.05), (528, 0.6), (1104, 0.3)])
+def test_bit_exact_camera_inside_the_point_cloud(cuda, size, offset):
+    """Every other scene looks at the head from 2.7 units away.  Here the camera sits inside it: about half of the Gaussians
+    are behind the near plane (culled at z <= 0.2, auxiliary.h:141-164), the ones just in front of it project to splats
+    of hundreds of pixels with centres far outside the image."""
+    P = 40_000
+    s = synthetic.raster_scene(P, size=size, fov_deg=40.0, seed_offset=size)
+    V = s["viewmatrix"].double()
+    proj = torch.linalg.inv(V) @ s["projmatrix"].double()
+    V2 = V.clone()
+    V2[3, :3] = torch.tensor([0.02, -0.03, offset], dtype=torch.float64)         # row-vector convention: translation in the last row
+    s["viewmatrix"] = V2.float().contiguous()
+    s["projmatrix"] = (V2 @ proj).float().contiguous()
+    s["campos"] = torch.linalg.inv(V2)[3, :3].float().contiguous()
+    s = to_dev(s, cuda)
+    ref = RefCuda().forward(s, cuda)
+    ours = run_ours(s, cuda)
+    culled = int((ref["radii"] == 0).sum())
+    assert 0.2 * P < culled < 0.97 * P, culled
+    assert int(ref["radii"].max()) > size // 2
+    assert_bit_exact(ours, ref, P)
+
+
+@pytest.mark.skipif(not ref_cuda_available(), reason="oracle/_ref/libggd_ref_cuda.so not present")
 @pytest.mark.parametrize("size", [256, 1104])
 def test_non_finite_and_absurd_gaussians_like_the_reference(cuda, size):
     """NaN / infinite means and opacities, and splats of astronomical size (their radius saturates the int it is stored in):
