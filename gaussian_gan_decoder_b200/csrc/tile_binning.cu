@@ -28,8 +28,9 @@
 //                     one per SM, walk the list of long tiles the scan wrote; lists beyond 24576 words are
 //                     sorted in depth chunks
 //   tile_sort_lazy_kernel   lean pipelines on large images: only the nearest depth chunk of every long list (the blend
-//                     reads 7-16 % of a dense frame's sorted instances); the tiles whose pixels outlive it are marked
-//                     by the blend, sorted completely (tile_sort_large_kernel, lazy = 2) and blended again
+//                     reads 7-16 % of a dense frame's sorted instances), cut at a depth bound estimated from a sample of
+//                     the list and gathered in one pass; the tiles whose pixels outlive it are marked by the blend,
+//                     sorted completely (tile_sort_large_kernel, lazy = 2) and blended again
 // Frames that do not qualify (a tile list longer than kTileSortHugeMax) take the radix path of binning.cu;
 // the decision is made on the device (counters[4]) and both sets of kernels are always enqueued, the
 // ones that do not apply return at once, so no host round trip is needed.
