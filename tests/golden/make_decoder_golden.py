@@ -25,6 +25,9 @@ CASES = {
     "eg3d_sequential_posenc": ("eg3d", "SequentialDecoder", True, 300, 16, 1),
     "panohead_reverse": ("panohead", "SequentialDecoderReverse", False, 700, 16, 3),
     "panohead_parallel_posenc": ("panohead", "ParallelDecoder", True, 300, 12, 3),
+    # plane_res may be (H, W); a seventh entry is rendering_kwargs["box_warp"] (1.0 above; the released PanoHead uses 0.7)
+    "panohead_sequential_boxwarp07": ("panohead", "SequentialDecoder", False, 500, 12, 3, 0.7),
+    "eg3d_reverse_nonsquare_boxwarp2": ("eg3d", "SequentialDecoderReverse", True, 300, (10, 18), 1, 2.0),
 }
 VARIANT = {"ParallelDecoder": "parallel", "SequentialDecoder": "sequential",
            "SequentialDecoderReverse": "sequential_reverse"}
@@ -39,10 +42,10 @@ class _Renderer:
 class StubG(torch.nn.Module):
     """Module-level (the reference's persistent_class pickles constructor arguments)."""
 
-    def __init__(self, planes, arch, depth, axes):
+    def __init__(self, planes, arch, depth, axes, box_warp=1.0):
         super().__init__()
         self.planes = planes
-        self.rendering_kwargs = {"box_warp": 1.0}
+        self.rendering_kwargs = {"box_warp": box_warp}
         if arch == "panohead":
             self.rendering_kwargs["triplane_depth"] = depth
         self.renderer = _Renderer(axes)
@@ -54,7 +57,7 @@ class StubG(torch.nn.Module):
         return {"feature_planes": self.planes}
 
 
-def run_arch(arch):
+def run_arch(arch, only=None):
     sys.path[:0] = [REF, os.path.join(REF, "main"), os.path.join(REF, "PanoHead" if arch == "panohead" else "eg3d")]
     from main.decoder_models.parallel_decoder import ParallelDecoder
     from main.decoder_models.sequential_decoder import SequentialDecoder
@@ -69,20 +72,22 @@ def run_arch(arch):
     classes = dict(ParallelDecoder=ParallelDecoder, SequentialDecoder=SequentialDecoder,
                    SequentialDecoderReverse=SequentialDecoderReverse)
 
-    for name, (a, cls, posenc, P, res, depth) in CASES.items():
-        if a != arch:
+    for name, (a, cls, posenc, P, res, depth, *rest) in CASES.items():
+        if a != arch or (only and name not in only):
             continue
+        box_warp = rest[0] if rest else 1.0
+        H, W = res if isinstance(res, tuple) else (res, res)
         g = torch.Generator().manual_seed(zlib.crc32(name.encode()) % 1000 + 7)
-        planes = torch.randn(1, 3, 32 * depth, res, res, generator=g)
+        planes = torch.randn(1, 3, 32 * depth, H, W, generator=g)
 
         torch.manual_seed(303)
-        dec = classes[cls](StubG(planes, arch, depth, generate_planes()), hidden_dim=128, use_xyz_embedding=posenc, use_gen_finetune=False, device="cpu")
+        dec = classes[cls](StubG(planes, arch, depth, generate_planes(), box_warp), hidden_dim=128, use_xyz_embedding=posenc, use_gen_finetune=False, device="cpu")
         if cls == "SequentialDecoderReverse":
             dec.triplane_sr = "None"      # reference quirk q1: attribute read but never set
         with torch.no_grad():
             for p in dec.parameters():
                 p.copy_(p.half().float())
-        xyz = (torch.rand(P, 3, generator=g) - 0.5) * 1.1     # a few points outside the box
+        xyz = (torch.rand(P, 3, generator=g) - 0.5) * 1.1 * box_warp     # a few points outside the box
         with torch.no_grad():
             out = dec(torch.zeros(1, 512), torch.zeros(1, 25), xyz, 1.0)
         flat = []
@@ -92,7 +97,7 @@ def run_arch(arch):
                 flat += [sd[f"backbone.{l}.weight"].reshape(-1), sd[f"backbone.{l}.bias"].reshape(-1)]
         flat = torch.cat(flat)
         assert torch.equal(flat, flat.half().float())
-        z = dict(arch=arch, variant=VARIANT[cls], pos_freqs=10 if posenc else 0, depth=depth,
+        z = dict(arch=arch, variant=VARIANT[cls], pos_freqs=10 if posenc else 0, depth=depth, box_warp=box_warp,
                  planes=planes.numpy(), xyz=xyz.numpy(), flat_fp16=flat.half().numpy())
         for h in HEADS:
             z["out_" + h] = out[h].numpy()
@@ -105,8 +110,8 @@ def run_arch(arch):
 
 
 if __name__ == "__main__":
-    if len(sys.argv) > 1:
-        run_arch(sys.argv[1])
-    else:
+    if len(sys.argv) > 1 and sys.argv[1] in ("eg3d", "panohead"):
+        run_arch(sys.argv[1], sys.argv[2:])
+    else:       # optional arguments: the names of the cases to (re)generate
         for arch in ("eg3d", "panohead"):
-            subprocess.check_call([sys.executable, os.path.abspath(__file__), arch])
+            subprocess.check_call([sys.executable, os.path.abspath(__file__), arch] + sys.argv[1:])

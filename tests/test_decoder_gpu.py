@@ -33,7 +33,7 @@ def check(out, ref, precision, tight=TIGHT):
 
 
 def build(case, dev):
-    G = StubG(case["planes"].to(dev), case["arch"], case["depth"])
+    G = StubG(case["planes"].to(dev), case["arch"], case["depth"], box_warp=case["box_warp"])
     dec = CLASSES[case["variant"]](G, hidden_dim=128, use_xyz_embedding=case["pos_freqs"] > 0,
                                    use_gen_finetune=False, device=dev)
     load_flat_into(dec, case["flat"])

@@ -12,14 +12,16 @@ import decoder_oracle as do  # noqa: E402
 
 
 def test_fixtures_present():
-    assert len(GOLDEN) >= 4
+    assert len(GOLDEN) >= 6
+    cases = [load(p) for p in GOLDEN]
+    assert any(c["box_warp"] != 1.0 for c in cases) and any(c["planes"].shape[-1] != c["planes"].shape[-2] for c in cases)
 
 
 @pytest.mark.parametrize("path", GOLDEN)
 def test_oracle_matches_reference_classes(path):
     c = load(path)
     with torch.no_grad():
-        res = do.decode(c["arch"], c["variant"], c["pos_freqs"], c["flat"], c["planes"], c["xyz"], 1.0, c["depth"])
+        res = do.decode(c["arch"], c["variant"], c["pos_freqs"], c["flat"], c["planes"], c["xyz"], c["box_warp"], c["depth"])
     for h in HEADS:
         err = (res[h] - c["out"][h]).abs().max().item()
         assert err <= 2e-6, (h, err)      # same ATen ops on the same machine: essentially exact

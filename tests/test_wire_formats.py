@@ -15,12 +15,14 @@ from gaussian_gan_decoder_b200.gaussian_renderer import GaussianModel
 HERE = os.path.dirname(os.path.abspath(__file__))
 CLS = {"eg3d_parallel": (ParallelDecoder, "eg3d", 1, False), "eg3d_sequential_posenc": (SequentialDecoder, "eg3d", 1, True),
        "panohead_reverse": (SequentialDecoderReverse, "panohead", 3, False),
-       "panohead_parallel_posenc": (ParallelDecoder, "panohead", 3, True)}
+       "panohead_parallel_posenc": (ParallelDecoder, "panohead", 3, True),
+       "panohead_sequential_boxwarp07": (SequentialDecoder, "panohead", 3, False),
+       "eg3d_reverse_nonsquare_boxwarp2": (SequentialDecoderReverse, "eg3d", 1, True)}
 
 
 def test_state_dict_keys_and_shapes_match_the_reference_classes():
     files = sorted(glob.glob(os.path.join(HERE, "golden", "state_dict_keys_*.json")))
-    assert len(files) == 4
+    assert len(files) == len(CLS)
     for path in files:
         name = os.path.basename(path)[len("state_dict_keys_"):-len(".json")]
         cls, arch, depth, posenc = CLS[name]
